@@ -1,0 +1,326 @@
+// C ABI of libchannel_b200 (include/channel_b200.h): handle life cycle, state
+// in/out in the reference layout, the RK3 driver entry points and the
+// operator-level drop-ins.  Host code only; kernels live in kernels_*.cu.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+#include "chan_internal.h"
+
+using namespace chan;
+
+static size_t csize(const chan_handle* h) { return 2 * (size_t)h->prec; }                      // bytes per complex
+static size_t field_bytes(const chan_handle* h) { return (size_t)h->d.ny * h->d.M * csize(h); } // compact field
+static size_t ref_bytes(const chan_handle* h) { return (size_t)h->d.nx * h->d.nz * h->d.ny * csize(h); }
+
+extern "C" int chan_partition(int n, int size, int rank, int* start, int* count) {
+  if (size <= 0 || rank < 0 || rank >= size || n < 0) return CHAN_ERR_ARG;
+  int q = n / size, r = n % size;
+  int s = rank * q + (rank < r ? rank : r);
+  int c = q + (rank < r ? 1 : 0);
+  if (start) *start = s;
+  if (count) *count = c;
+  return CHAN_OK;
+}
+extern "C" int chan_active_kx(int nx) { return 2 * (nx / 3) + 1; }
+extern "C" int chan_active_kz(int nz) { return (2 * nz - 2) / 3 + 1; }
+
+extern "C" int chan_config_default(chan_config* c) {
+  if (!c) return CHAN_ERR_ARG;
+  memset(c, 0, sizeof(*c));
+  c->nx = 128; c->ny = 128; c->nz = 65;            // run.conf:3-5
+  c->precision = 8;
+  c->reynolds = 3250.0; c->qvelocity = 1.8; c->cfl = 0.5;
+  c->rank = 0; c->size = 1; c->device = -1; c->plane_batch = 0;
+  return CHAN_OK;
+}
+
+static int alloc_dev(chan_handle* h, void** p, size_t bytes) {
+  if (cudaMalloc(p, bytes) != cudaSuccess) { cudaGetLastError(); return set_err(h, CHAN_ERR_ALLOC, "cudaMalloc of %zu bytes failed", bytes); }
+  CHAN_CUDA(h, cudaMemsetAsync(*p, 0, bytes, h->stream));
+  return CHAN_OK;
+}
+
+extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
+  if (!cfg || !out) return CHAN_ERR_ARG;
+  *out = 0;
+  chan_handle* h = new (std::nothrow) chan_handle;
+  if (!h) return CHAN_ERR_ALLOC;
+  memset(h, 0, sizeof(*h));
+  *out = h;                                         // returned even on failure so the caller can read the message
+  h->cfg = *cfg;
+  if (cfg->precision != 4 && cfg->precision != 8) return set_err(h, CHAN_ERR_ARG, "precision must be 4 or 8, got %d", cfg->precision);
+  if (cfg->nx < 8 || cfg->ny < 8 || cfg->nz < 5 || (cfg->nx & 1)) return set_err(h, CHAN_ERR_ARG, "grid %dx%dx%d: need even NX>=8, NY>=8, NZ>=5", cfg->nx, cfg->ny, cfg->nz);
+  if (cfg->size != 1 || cfg->rank != 0) return set_err(h, CHAN_ERR_ARG, "this build runs one slab per handle; multi-GPU runs go through the python launcher");
+  h->prec = cfg->precision;
+  Dims& d = h->d;
+  d.nx = cfg->nx; d.ny = cfg->ny; d.nz = cfg->nz; d.nzp = 2 * cfg->nz - 2;
+  d.kxmax = d.nx / 3; d.Kx = 2 * d.kxmax + 1; d.Kz = d.nzp / 3 + 1;          // dealias.cu:37 (integer divisions)
+  if (d.Kz > d.nz - 1 || d.kxmax >= d.nx / 2) return set_err(h, CHAN_ERR_ARG, "grid too small for the 2/3 rule");
+  d.ikx0 = 0; d.Kxl = d.Kx; d.j0 = 0; d.nyl = d.ny; d.M = (long)d.Kxl * d.Kz;
+  if (cfg->device >= 0) CHAN_CUDA(h, cudaSetDevice(cfg->device));
+  CHAN_CUDA(h, cudaGetDevice(&h->device));
+  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  int rc;
+  const size_t fb = field_bytes(h);
+  void** fields[11] = { &h->phi, &h->g, &h->v, &h->dv, &h->Rphi, &h->Rg, &h->u, &h->w, &h->ox, &h->oy, &h->oz };
+  for (int i = 0; i < 11; i++) if ((rc = alloc_dev(h, fields[i], fb))) return rc;
+  const size_t chain = (size_t)d.ny * 2 * d.M * sizeof(double);
+  if ((rc = alloc_dev(h, (void**)&h->sA, chain))) return rc;
+  if ((rc = alloc_dev(h, (void**)&h->sB, chain))) return rc;
+  if ((rc = alloc_dev(h, (void**)&h->sC, chain))) return rc;
+  if ((rc = alloc_dev(h, (void**)&h->sP, chain / 2))) return rc;
+  // plane batch: keep the x-transformed staging of one batch (6 fields) inside the L2
+  const size_t plane_q = (size_t)6 * d.nx * d.Kz * csize(h);
+  int pb = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(48u << 20) / plane_q);
+  if (pb < 1) pb = 1;
+  if (pb > d.nyl) pb = d.nyl;
+  h->plane_batch = pb;
+  if ((rc = alloc_dev(h, &h->Q, plane_q * pb))) return rc;
+  const size_t rb = (size_t)d.ny * h->prec;
+  if ((rc = alloc_dev(h, &h->mean_u, rb))) return rc;
+  if ((rc = alloc_dev(h, &h->mean_N, rb))) return rc;
+  if ((rc = alloc_dev(h, &h->mean_uw, rb))) return rc;
+  if ((rc = alloc_dev(h, &h->mean_tmp, 6 * rb))) return rc;
+  if ((rc = alloc_dev(h, (void**)&h->sc, sizeof(Scalars)))) return rc;
+  h->io_bytes = ref_bytes(h);
+  if ((rc = alloc_dev(h, &h->io_buf, h->io_bytes))) return rc;
+  if ((rc = build_tables(h))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+
+extern "C" void chan_destroy(chan_handle* h) {
+  if (!h) return;
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
+                   h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
+                   h->mean_uw, h->mean_tmp, h->sc, h->io_buf };
+  for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+extern "C" const char* chan_last_error(const chan_handle* h) { return h ? h->err : "null handle"; }
+extern "C" long chan_launch_count(const chan_handle* h) { return h ? h->launches : 0; }
+extern "C" int chan_sync(chan_handle* h) { if (!h) return CHAN_ERR_ARG; CHAN_CUDA(h, cudaStreamSynchronize(h->stream)); return CHAN_OK; }
+
+static void* field_ptr(chan_handle* h, int which) {
+  void* t[CHAN_F_COUNT] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz };
+  return (which >= 0 && which < CHAN_F_COUNT) ? t[which] : 0;
+}
+
+extern "C" int chan_set_field(chan_handle* h, int which, const void* host) {
+  if (!h || !host) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  CHAN_CUDA(h, cudaMemcpyAsync(h->io_buf, host, ref_bytes(h), cudaMemcpyHostToDevice, h->stream));
+  int rc = launch_pack(h, h->io_buf, f); if (rc) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_get_field(chan_handle* h, int which, void* host) {
+  if (!h || !host) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  int rc = launch_unpack(h, f, h->io_buf); if (rc) return rc;
+  CHAN_CUDA(h, cudaMemcpyAsync(host, h->io_buf, ref_bytes(h), cudaMemcpyDeviceToHost, h->stream));
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_set_fields(chan_handle* h, const void* ddv, const void* g) {
+  int rc = chan_set_field(h, CHAN_F_DDV, ddv); if (rc) return rc;
+  return chan_set_field(h, CHAN_F_G, g);
+}
+extern "C" int chan_get_fields(chan_handle* h, void* ddv, void* g) {
+  int rc = chan_get_field(h, CHAN_F_DDV, ddv); if (rc) return rc;
+  return chan_get_field(h, CHAN_F_G, g);
+}
+
+extern "C" int chan_set_umean(chan_handle* h, const void* um) {
+  if (!h || !um) return CHAN_ERR_ARG;
+  const int ny = h->d.ny;
+  if (h->prec == 4) { float* t = (float*)malloc(sizeof(float) * ny); for (int j = 0; j < ny; j++) t[j] = ((const float*)um)[2 * j];
+    cudaError_t e = cudaMemcpy(h->mean_u, t, sizeof(float) * ny, cudaMemcpyHostToDevice); free(t); CHAN_CUDA(h, e); }
+  else { double* t = (double*)malloc(sizeof(double) * ny); for (int j = 0; j < ny; j++) t[j] = ((const double*)um)[2 * j];
+    cudaError_t e = cudaMemcpy(h->mean_u, t, sizeof(double) * ny, cudaMemcpyHostToDevice); free(t); CHAN_CUDA(h, e); }
+  return CHAN_OK;
+}
+extern "C" int chan_get_umean(chan_handle* h, void* um) {
+  if (!h || !um) return CHAN_ERR_ARG;
+  const int ny = h->d.ny;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (h->prec == 4) { float* t = (float*)malloc(sizeof(float) * ny);
+    cudaError_t e = cudaMemcpy(t, h->mean_u, sizeof(float) * ny, cudaMemcpyDeviceToHost);
+    for (int j = 0; j < ny; j++) { ((float*)um)[2 * j] = t[j]; ((float*)um)[2 * j + 1] = 0.0f; } free(t); CHAN_CUDA(h, e); }
+  else { double* t = (double*)malloc(sizeof(double) * ny);
+    cudaError_t e = cudaMemcpy(t, h->mean_u, sizeof(double) * ny, cudaMemcpyDeviceToHost);
+    for (int j = 0; j < ny; j++) { ((double*)um)[2 * j] = t[j]; ((double*)um)[2 * j + 1] = 0.0; } free(t); CHAN_CUDA(h, e); }
+  return CHAN_OK;
+}
+extern "C" int chan_get_nmean(chan_handle* h, double* out) {
+  if (!h || !out) return CHAN_ERR_ARG;
+  const int ny = h->d.ny;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (h->prec == 4) { float* t = (float*)malloc(sizeof(float) * ny);
+    cudaError_t e = cudaMemcpy(t, h->mean_N, sizeof(float) * ny, cudaMemcpyDeviceToHost);
+    for (int j = 0; j < ny; j++) out[j] = t[j]; free(t); CHAN_CUDA(h, e); }
+  else CHAN_CUDA(h, cudaMemcpy(out, h->mean_N, sizeof(double) * ny, cudaMemcpyDeviceToHost));
+  return CHAN_OK;
+}
+
+extern "C" int chan_get_scalars(chan_handle* h, chan_scalars* out) {
+  if (!h || !out) return CHAN_ERR_ARG;
+  Scalars s;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  CHAN_CUDA(h, cudaMemcpy(&s, h->sc, sizeof(s), cudaMemcpyDeviceToHost));
+  out->dt = s.dt; out->dt_next = s.dt_next; out->dt_c = s.dt_c; out->dt_v = s.dt_v;
+  for (int c = 0; c < 3; c++) out->umax[c] = s.umax[c];
+  out->utau[0] = s.utau[0]; out->utau[1] = s.utau[1];
+  out->counter = s.counter;
+  return CHAN_OK;
+}
+static int poke_scalar(chan_handle* h, size_t off, double v) {
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  CHAN_CUDA(h, cudaMemcpy((char*)h->sc + off, &v, sizeof(double), cudaMemcpyHostToDevice));
+  return CHAN_OK;
+}
+extern "C" int chan_set_fixed_dt(chan_handle* h, double dt) { if (!h) return CHAN_ERR_ARG; return poke_scalar(h, offsetof(Scalars, fixed_dt), dt); }
+extern "C" int chan_set_dt(chan_handle* h, double dt) {
+  if (!h) return CHAN_ERR_ARG;
+  double r = h->prec == 4 ? (double)(float)dt : dt;
+  return poke_scalar(h, offsetof(Scalars, dt), r);
+}
+
+// ---- hot path ---------------------------------------------------------------------
+extern "C" int chan_rk_init(chan_handle* h) {
+  if (!h) return CHAN_ERR_ARG;
+  // dealias x2 (RK3.c:120-121) is structural; imposeSymetry (RK3.c:122); calcVdV (RK3.c:123)
+  int rc = launch_symmetrize(h, h->phi, h->g); if (rc) return rc;
+  return launch_op(h, OP_VDV, h->phi, h->v, h->dv, 0.0, 0.0);
+}
+
+extern "C" int chan_rk_substep(chan_handle* h, int n) {
+  if (!h || n < 0 || n > 2) return CHAN_ERR_ARG;
+  int rc;
+  if ((rc = launch_pencil_pre(h))) return rc;            // calcUW + writeUmean + d/dy + calcOmega
+  if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
+  if ((rc = launch_scalar_stage(h, n))) return rc;        // mean flow, calcDt
+  return launch_pencil_post(h, n);                        // RK explicit + h_v,h_g + implicit + bi-Laplacian
+}
+
+extern "C" int chan_rk_end_step(chan_handle* h) {
+  if (!h) return CHAN_ERR_ARG;
+  int rc;
+  if (h->host_counter % 1000 == 0) { if ((rc = launch_symmetrize(h, h->phi, h->g))) return rc; }   // RK3.c:174-176
+  h->host_counter++;
+  return launch_end_step(h);
+}
+
+extern "C" int chan_rk_step(chan_handle* h, int nsteps) {
+  if (!h || nsteps < 0) return CHAN_ERR_ARG;
+  for (int s = 0; s < nsteps; s++) {
+    for (int n = 0; n < 3; n++) { int rc = chan_rk_substep(h, n); if (rc) return rc; }
+    int rc = chan_rk_end_step(h); if (rc) return rc;
+  }
+  return CHAN_OK;
+}
+
+extern "C" int chan_statistics(chan_handle* h, double* out) {
+  if (!h || !out) return CHAN_ERR_ARG;
+  double* d; const size_t b = sizeof(double) * 4 * h->d.ny;
+  CHAN_CUDA(h, cudaMalloc(&d, b));
+  int rc = launch_stats(h, d);
+  if (!rc) { cudaError_t e = cudaMemcpyAsync(out, d, b, cudaMemcpyDeviceToHost, h->stream); if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) rc = set_err(h, CHAN_ERR_CUDA, "statistics copy: %s", cudaGetErrorString(e)); }
+  cudaFree(d);
+  return rc;
+}
+
+// ---- operator level: device pointers, reference layout, in place ----------------------
+// work fields used as compact staging: u, w, ox, oy, oz (never live across API calls)
+static int op_inplace(chan_handle* h, int op, void* a_dev, void* b_dev, void* c_dev, int nin, int nout, double betha, double dt) {
+  void* st[3] = { h->ox, h->oy, h->oz };
+  void* ext[3] = { a_dev, b_dev, c_dev };
+  int rc;
+  for (int i = 0; i < nin; i++) if ((rc = launch_pack(h, ext[i], st[i]))) return rc;
+  if ((rc = launch_op(h, op, st[0], st[1], st[2], betha, dt))) return rc;
+  for (int i = 0; i < nout; i++) if ((rc = launch_unpack(h, st[i], ext[i]))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+
+extern "C" int chan_dealias(chan_handle* h, void* u) {
+  if (!h || !u) return CHAN_ERR_ARG;
+  int rc = launch_pack(h, u, h->ox); if (rc) return rc;
+  if ((rc = launch_unpack(h, h->ox, u))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_deriv_y(chan_handle* h, void* u) { if (!h || !u) return CHAN_ERR_ARG; return op_inplace(h, OP_DERIV_Y, u, 0, 0, 1, 1, 0, 0); }
+extern "C" int chan_deriv_yy(chan_handle* h, void* u) { if (!h || !u) return CHAN_ERR_ARG; return op_inplace(h, OP_DERIV_YY, u, 0, 0, 1, 1, 0, 0); }
+extern "C" int chan_helmholtz(chan_handle* h, void* u) { if (!h || !u) return CHAN_ERR_ARG; return op_inplace(h, OP_HELM, u, 0, 0, 1, 1, 0, 0); }
+extern "C" int chan_implicit(chan_handle* h, void* u, double betha, double dt) { if (!h || !u) return CHAN_ERR_ARG; return op_inplace(h, OP_IMPLICIT, u, 0, 0, 1, 1, betha, dt); }
+extern "C" int chan_bilaplacian(chan_handle* h, void* ddv, void* v, void* dv, double betha, double dt) {
+  if (!h || !ddv || !v || !dv) return CHAN_ERR_ARG;
+  void* ext[3] = { ddv, v, dv }; void* st[3] = { h->ox, h->oy, h->oz };
+  int rc = launch_pack(h, ddv, st[0]); if (rc) return rc;
+  if ((rc = launch_op(h, OP_BILAP, st[0], st[1], st[2], betha, dt))) return rc;
+  for (int i = 0; i < 3; i++) if ((rc = launch_unpack(h, st[i], ext[i]))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_calc_uw(chan_handle* h, void* ux, void* uz, const void* f, const void* g) {
+  if (!h || !ux || !uz || !f || !g) return CHAN_ERR_ARG;
+  int rc = launch_pack(h, f, h->ox); if (rc) return rc;
+  if ((rc = launch_pack(h, g, h->oy))) return rc;
+  if ((rc = launch_op(h, OP_UW, h->ox, h->oy, 0, 0, 0))) return rc;       // -> h->u, h->w
+  if ((rc = launch_unpack(h, h->u, ux))) return rc;
+  if ((rc = launch_unpack(h, h->w, uz))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_convolution(chan_handle* h, void* ux, void* uy, void* uz, void* wx, void* wy, void* wz) {
+  if (!h || !ux || !uy || !uz || !wx || !wy || !wz) return CHAN_ERR_ARG;
+  // uses the state slot v as staging for uy: save and restore it through the scratch field sC
+  int rc;
+  const size_t fb = field_bytes(h);
+  CHAN_CUDA(h, cudaMemcpyAsync(h->sC, h->v, fb, cudaMemcpyDeviceToDevice, h->stream));
+  if ((rc = launch_pack(h, ux, h->u))) return rc;
+  if ((rc = launch_pack(h, uy, h->v))) return rc;
+  if ((rc = launch_pack(h, uz, h->w))) return rc;
+  if ((rc = launch_op(h, OP_OMEGA, 0, 0, 0, 0, 0))) return rc;            // d/dy u, d/dy w, omega
+  if ((rc = launch_nonlinear_planes(h))) return rc;
+  CHAN_CUDA(h, cudaMemcpyAsync(h->v, h->sC, fb, cudaMemcpyDeviceToDevice, h->stream));
+  if ((rc = launch_unpack(h, h->ox, wx))) return rc;
+  if ((rc = launch_unpack(h, h->oy, wy))) return rc;
+  if ((rc = launch_unpack(h, h->oz, wz))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_calc_hvg(chan_handle* h, void* nlx, void* nly, void* nlz) {
+  if (!h || !nlx || !nly || !nlz) return CHAN_ERR_ARG;
+  void* ext[3] = { nlx, nly, nlz }; void* st[3] = { h->ox, h->oy, h->oz };
+  int rc;
+  for (int i = 0; i < 3; i++) if ((rc = launch_pack(h, ext[i], st[i]))) return rc;
+  if ((rc = launch_op(h, OP_HVG, st[0], st[1], st[2], 0, 0))) return rc;
+  if ((rc = launch_unpack(h, st[0], nlx))) return rc;
+  if ((rc = launch_unpack(h, st[2], nlz))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_impose_symmetry(chan_handle* h, void* u, void* v) {
+  if (!h || !u || !v) return CHAN_ERR_ARG;
+  int rc = launch_pack(h, u, h->ox); if (rc) return rc;
+  if ((rc = launch_pack(h, v, h->oy))) return rc;
+  if ((rc = launch_symmetrize(h, h->ox, h->oy))) return rc;
+  if ((rc = launch_unpack(h, h->ox, u))) return rc;
+  if ((rc = launch_unpack(h, h->oy, v))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_fft_backward_transpose(chan_handle* h, const void* u, void* phys) {
+  if (!h || !u || !phys) return CHAN_ERR_ARG;
+  int rc = launch_pack(h, u, h->ox); if (rc) return rc;
+  if ((rc = launch_to_physical(h, h->ox, phys))) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}

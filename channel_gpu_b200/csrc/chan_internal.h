@@ -1,0 +1,125 @@
+// Internal declarations of libchannel_b200 (not installed; the public C ABI is
+// include/channel_b200.h).
+//
+// DATA LAYOUT.  Every spectral field is stored COMPACT and
+// PLANE-MAJOR:  F[j][m],  m = ikx*Kz + kz,  complex T2, with
+//   ikx in [0,Kx)  the 2*floor(NX/3)+1 active kx of the 2/3 rule (dealias.cu:37):
+//                  kx = ikx <= kxmax ? ikx : ikx - Kx,
+//   kz  in [0,Kz)  Kz = floor((2NZ-2)/3)+1,
+//   j   in [0,NY)  the wall-normal index (slowest).
+// One y-plane of all active modes is contiguous, so the x/z FFT kernels read
+// planes directly (no y-pencil <-> xz-plane transpose on one GPU), and the
+// y-solves run one thread per REAL chain (mode, re|im) with the 32 lanes of a
+// warp on 32 consecutive reals of a plane row: fully coalesced.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/channel_b200.h"
+
+namespace chan {
+
+template <typename T> struct Vec2;
+template <> struct Vec2<float>  { typedef float2  type; };
+template <> struct Vec2<double> { typedef double2 type; };
+
+// ---- y tables -------------------------------------------------------------
+// Direction-generic coefficient tables, indexed by SWEEP position jj.  A sweep
+// with dir=0 walks j = jj (up), dir=1 walks j = NY-1-jj (down).
+struct D1Tab {            // compact first derivative, fixed matrix, LU folded in
+  const double *eP, *eC, *eN;   // rhs weights (prev, centre, next in sweep) * pivot
+  const double *eL;             // lower * pivot   (multiplies d'[jj-1])
+  const double *cp;             // upper * pivot   (back substitution)
+};
+struct D2Tab {            // second-derivative compact weights (Helmholtz / implicit)
+  const double *rP, *rN;        // rhs weights of prev / next in sweep (alpha2 / beta2)
+  const double *wP, *wC, *wN;   // operator weights of prev / centre / next (B2 | A2, C2)
+};
+struct YTabs {
+  D1Tab d1[2];
+  D2Tab d2[2];
+  const double* y;              // Fmesh(j*DELTA_Y-1.0), physical j
+};
+
+// ---- FFT plan -------------------------------------------------------------
+struct FftPlan {
+  int n;
+  int nstage;
+  int radix[16];
+  int span[16];                 // sub-transform size entering stage t (1, r0, r0*r1, ...)
+  const void* tw;               // T2[n]: exp(-2 pi i k / n)
+};
+
+// ---- handle ---------------------------------------------------------------
+struct Dims {
+  int nx, ny, nz, nzp;          // NZ = complex z count, nzp = 2NZ-2 physical z points
+  int kxmax, Kx, Kz;            // active-mode box
+  int ikx0, Kxl;                // this rank's active-kx slab (pencil stages)
+  int j0, nyl;                  // this rank's y-plane slab (plane stages)
+  long M;                       // Kxl*Kz modes per plane row held by the pencil stages
+};
+
+struct Scalars {                // device-resident step scalars (doubles hold T-rounded values)
+  double dt;                    // dt of the current step (one-step lag, RK3.c:114,179)
+  double dt_next;               // calcDt of substep 0 (RK3.c:143-145)
+  double dt_c, dt_v;
+  double fixed_dt;              // >0: injected instead of calcDt
+  unsigned long long umax_bits[3];   // max |u|,|v|,|w| over physical points, as ordered bits
+  double umax[3];               // the same maxima as sampled at substep 0 (what calcDt used)
+  double dudy_wall[2];          // d<u>/dy at j=0, NY-1 (convolution.c:14-16)
+  double utau[2];
+  int    counter;
+};
+
+}  // namespace chan
+
+struct chan_handle {
+  int prec;                     // 4 | 8 : sizeof(state real)
+  chan::Dims d;
+  chan_config cfg;
+  int device;
+  cudaStream_t stream;
+  // state + work fields, compact plane-major, complex T
+  void *phi, *g, *v, *dv, *Rphi, *Rg;
+  void *u, *w, *ox, *oy, *oz;
+  // y-solve scratch: 3 real chains [NY][2M] + pivots [NY][M], double
+  double *sA, *sB, *sC, *sP;
+  // plane-stage staging Q[f][jb][p][kz], complex T
+  void* Q; int plane_batch;
+  // tables
+  double* ytab_store; chan::YTabs yt;
+  void *tw_x, *tw_z; chan::FftPlan px, pz;
+  int *invx, *invz;             // digit-reversed position -> natural index (export path only)
+  void *mean_a, *mean_b;        // host-mesh differences in T (meanUevol.c:230-231)
+  void *mean_u, *mean_N, *mean_uw, *mean_tmp;   // T[NY] (+ scratch)
+  chan::Scalars* sc;            // device
+  // boundary staging (reference layout <-> compact)
+  void* io_buf; size_t io_bytes;
+  long launches;                // kernels launched so far (bench's gpu_launches)
+  long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
+  char err[256];
+};
+
+namespace chan {
+enum { OP_DERIV_Y = 1, OP_DERIV_YY, OP_HELM, OP_IMPLICIT, OP_BILAP, OP_VDV, OP_UW, OP_HVG, OP_OMEGA };
+int set_err(chan_handle* h, int code, const char* fmt, ...);
+#define CHAN_CUDA(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+  return chan::set_err(h, CHAN_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+// kernels_tables.cu
+int build_tables(chan_handle* h);
+// kernels_pencil.cu
+int launch_pencil_pre(chan_handle* h);
+int launch_pencil_post(chan_handle* h, int n);
+int launch_op(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt);
+// kernels_plane.cu
+int launch_nonlinear_planes(chan_handle* h);                 // u,v,w,omega -> H (in ox,oy,oz)
+int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields
+int launch_to_physical(chan_handle* h, const void* f, void* phys_out);   // debug/parity: one field -> real [NY][NX][nzp]
+// kernels_misc.cu
+int launch_pack(chan_handle* h, const void* ref_layout_dev, void* compact);      // [i][k][j] -> [j][m]
+int launch_unpack(chan_handle* h, const void* compact, void* ref_layout_dev);    // [j][m] -> [i][k][j] (zeros outside)
+int launch_scalar_stage(chan_handle* h, int n);              // mean flow, dt, bookkeeping
+int launch_end_step(chan_handle* h);
+int launch_stats(chan_handle* h, double* out4ny_dev);
+}  // namespace chan

@@ -1,0 +1,554 @@
+// Wall-normal (y) stages of the RK3 substep: every compact-FD derivative and
+// every tridiagonal Helmholtz / implicit / "bi-Laplacian" solve, fused with the
+// pointwise spectral algebra around them.
+//
+// One thread owns one REAL chain: (mode m, component c = re|im) for all NY rows.
+// The matrices are real, so the complex solves of the reference (cuSPARSE
+// ZgtsvStridedBatch on complex right-hand sides, derivatives_nu_double.cu:406)
+// split into two independent real Thomas sweeps.  Rows are plane-major
+// (chan_internal.h), so at every sweep step the 32 lanes of a warp touch 32
+// consecutive reals: 128/256-byte fully coalesced transactions, no shared
+// memory, no transposes, any NY.
+//
+// Sweeps alternate direction: the back-substitution of solve k runs in the same
+// direction as the elimination of solve k+1, so both are fused in ONE pass over
+// y (the elimination lags one row behind).  Forward-sweep intermediates go to
+// the fp64 scratch arrays sA/sB/sC (+ pivots sP) and are read back by the very
+// thread that wrote them.  The compact first-derivative matrix is the same for
+// every mode: its LU is folded into the y tables once (kernels_tables.cu); the
+// Helmholtz / implicit pivots depend on kk and are formed on the fly.
+//
+// Reference semantics mirrored here (file:line under /root/reference/src):
+//   pencil_pre   = calcUW (nonLinear_kernels.cu:8-92) + writeUmean
+//                  (meanUevol.c:117-125) + the two deriv_Y of convolution.c:7-11
+//                  + readUtau (:14-16) + calcOmega (convolution_kernels.cu:7-66)
+//   pencil_post  = RKstep_1 (RK3_kernels.cu:155-177) + calcHvg
+//                  (nonLinear_kernels.cu:212-232) + RKstep_2 (:179-194) +
+//                  implicitSolver_double + bilaplaSolver_double
+//                  (implicitStep_nu_double.cu:227, bilplacSolver_double.cu:320)
+//                  + the copies/dealias of RK3.c:161-166 (dealias is structural
+//                  here: truncated modes are not stored)
+// The state type T rounds exactly where the reference's cast_kernel does (after
+// every solve) and where its pointwise kernels compute in float.
+#include "chan_internal.h"
+
+namespace chan {
+
+template <typename T>
+struct PArgs {
+  typedef typename Vec2<T>::type T2;
+  T2 *phi, *g, *v, *dv, *Rphi, *Rg, *u, *w, *ox, *oy, *oz;
+  double *sA, *sB, *sC, *sP;
+  const T* mean_u;
+  Scalars* sc;
+  YTabs yt;
+  int ny, Kz, ikx0, kxmax, Kx;
+  long M;
+  T k1fac, k3fac;          // PI2/LX, PI2/LZ in the state type (RK3_kernels.cu:53-54)
+  T nuT;                   // 1.0f/REYNOLDS in the state type (RK3_kernels.cu:58)
+  double nuD;              // 1.0/REYNOLDS in double (implicitStep_nu_double.cu:133)
+  double reD;              // (double)REYNOLDS (bilplacSolver_double.cu:58)
+  int n;                   // RK substep
+  T alpha, dseda, gammad, betha;
+  // generic operator launches
+  int op; T2 *f0, *f1, *f2; T op_betha, op_dt; int use_mean;
+};
+
+struct Mode {
+  long m; int c; long e;   // mode, component, real chain index
+  int kxi, kzi; bool zero_mode;
+};
+
+template <typename T>
+struct Wave { T k1, k3, kk; double kkd; T sc; T sp; };   // sc = sign of own component of i*z: -1 (re), +1 (im)
+
+template <typename T>
+__device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) {
+  long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= 2 * a.M) return false;
+  md.e = e; md.m = e >> 1; md.c = (int)(e & 1);
+  int ikx = a.ikx0 + (int)(md.m / a.Kz);
+  md.kzi = (int)(md.m % a.Kz);
+  md.kxi = ikx <= a.kxmax ? ikx : ikx - a.Kx;
+  md.zero_mode = (md.kxi == 0 && md.kzi == 0);
+  wv.k1 = a.k1fac * (T)md.kxi;
+  wv.k3 = a.k3fac * (T)md.kzi;
+  wv.kk = wv.k1 * wv.k1 + wv.k3 * wv.k3;
+  double k1d = (double)a.k1fac * (double)md.kxi, k3d = (double)a.k3fac * (double)md.kzi;
+  wv.kkd = k1d * k1d + k3d * k3d;
+  wv.sc = md.c ? (T)1 : (T)-1;
+  wv.sp = -wv.sc;
+  return true;
+}
+
+__device__ __forceinline__ int phys_row(int dir, int jj, int ny) { return dir ? ny - 1 - jj : jj; }
+
+template <typename T2, typename T>
+__device__ __forceinline__ T own(const T2& z, int c) { return c ? z.y : z.x; }
+template <typename T2, typename T>
+__device__ __forceinline__ T other(const T2& z, int c) { return c ? z.x : z.y; }
+
+// ---- fixed-matrix compact d/dy: elimination with the folded LU ---------------
+struct ElimD1 {
+  double f1, f2, dprev;
+  __device__ __forceinline__ void step(const D1Tab& t, int dir, int jj, int ny, double f,
+                                       double* s, long stride, long e) {
+    if (jj == 0) { f2 = f; return; }
+    if (jj == 1) { f1 = f; return; }
+    if (jj == 2) {
+      double d0 = __ldg(t.eC) * f2 + __ldg(t.eN) * f1 + __ldg(t.eP) * f;
+      s[(long)phys_row(dir, 0, ny) * stride + e] = d0; dprev = d0;
+    }
+    int r = jj - 1;
+    double d = __ldg(t.eP + r) * f2 + __ldg(t.eC + r) * f1 + __ldg(t.eN + r) * f - __ldg(t.eL + r) * dprev;
+    s[(long)phys_row(dir, r, ny) * stride + e] = d; dprev = d;
+    if (jj == ny - 1) {
+      double dl = __ldg(t.eC + jj) * f + __ldg(t.eP + jj) * f1 + __ldg(t.eN + jj) * f2 - __ldg(t.eL + jj) * dprev;
+      s[(long)phys_row(dir, jj, ny) * stride + e] = dl;
+    }
+    f2 = f1; f1 = f;
+  }
+};
+
+// ---- kk-dependent Helmholtz / implicit matrices: pivots on the fly, NR right-hand sides
+template <int NR>
+struct ElimVar {
+  double f1[NR], f2[NR], dprev[NR], cprev;
+  // implicit: (M - D(A - kk M)) x = M f ; helmholtz: (A - kk M) x = M f   (hemholzt_nu_double.cu:156-163,
+  // implicitStep_nu_double.cu:156-163); wall rows are identity with zero rhs (:167-185)
+  __device__ __forceinline__ void step(const D2Tab& t, int dir, int jj, int ny, const double (&f)[NR],
+                                       bool implicit, double kk, double D,
+                                       double* const (&s)[NR], long stride, long e,
+                                       double* sp, long M, long m) {
+    if (jj == 0) {
+#pragma unroll
+      for (int q = 0; q < NR; q++) f2[q] = f[q];
+      return;
+    }
+    if (jj == 1) {
+      long r0 = phys_row(dir, 0, ny);
+#pragma unroll
+      for (int q = 0; q < NR; q++) { f1[q] = f[q]; s[q][r0 * stride + e] = 0.0; dprev[q] = 0.0; }
+      sp[r0 * M + m] = 0.0; cprev = 0.0;
+      return;
+    }
+    int r = jj - 1;
+    double rP = __ldg(t.rP + r), rN = __ldg(t.rN + r);
+    double wP = __ldg(t.wP + r), wC = __ldg(t.wC + r), wN = __ldg(t.wN + r);
+    double lo, di, up;
+    if (implicit) { lo = rP - D * wP + D * kk * rP; di = 1.0 - D * wC + D * kk * 1.0; up = rN - D * wN + D * kk * rN; }
+    else          { lo = wP - kk * rP;              di = wC - kk;                     up = wN - kk * rN; }
+    if (r == 1) lo = 0.0;
+    if (r == ny - 2) up = 0.0;
+    double piv = 1.0 / (di - lo * cprev);
+    double cp = up * piv;
+    long rr = phys_row(dir, r, ny);
+#pragma unroll
+    for (int q = 0; q < NR; q++) {
+      double rhs = rN * f[q] + f1[q] + rP * f2[q];
+      double d = (rhs - lo * dprev[q]) * piv;
+      s[q][rr * stride + e] = d; dprev[q] = d;
+      f2[q] = f1[q]; f1[q] = f[q];
+    }
+    sp[rr * M + m] = cp; cprev = cp;
+    if (jj == ny - 1) {
+      long rl = phys_row(dir, jj, ny);
+#pragma unroll
+      for (int q = 0; q < NR; q++) s[q][rl * stride + e] = 0.0;
+      sp[rl * M + m] = 0.0;
+    }
+  }
+};
+
+template <typename T> __device__ __forceinline__ double rnd(double x) { return (double)(T)x; }
+
+// ---- unfused building blocks (operator-level API, calcVdV) -------------------
+// out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
+template <typename T>
+__device__ void d1_solve(const PArgs<T>& a, const Mode& md, const T* __restrict__ in, T* __restrict__ out, double* s) {
+  const long st = 2 * a.M; const int ny = a.ny;
+  __syncwarp();
+  ElimD1 el;
+  for (int jj = 0; jj < ny; jj++) el.step(a.yt.d1[0], 0, jj, ny, (double)in[(long)jj * st + md.e], s, st, md.e);
+  double x = 0.0;
+  for (int j = ny - 1; j >= 0; j--) {
+    x = s[(long)j * st + md.e] - __ldg(a.yt.d1[0].cp + j) * x;
+    out[(long)j * st + md.e] = (T)x;
+  }
+}
+template <typename T>
+__device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, bool implicit, double D,
+                          const T* __restrict__ in, T* __restrict__ out, double* s, double* sp) {
+  const long st = 2 * a.M; const int ny = a.ny;
+  __syncwarp();   // the pivot row is shared by the two components of a mode
+  ElimVar<1> el;
+  double* const ss[1] = { s };
+  for (int jj = 0; jj < ny; jj++) {
+    const double f[1] = { (double)in[(long)jj * st + md.e] };
+    el.step(a.yt.d2[0], 0, jj, ny, f, implicit, wv.kkd, D, ss, st, md.e, sp, a.M, md.m);
+  }
+  double x = 0.0;
+  for (int j = ny - 1; j >= 0; j--) {
+    x = s[(long)j * st + md.e] - sp[(long)j * a.M + md.m] * x;
+    out[(long)j * st + md.e] = (T)x;
+  }
+}
+
+// ---- wall correction of the bi-Laplacian (setBoundaryCond, bilplacSolver_double.cu:6-296)
+struct BcFun { double v1, v2, dv1, dv2, ddv1, ddv2; };
+// the six functions exactly as written at :174-217: half of the exponentials are fp32 `expf`,
+// and the l2 lines take exp(-l1*(1+y)) in their first bracket — mirrored, it
+// defines the reference's v.
+__device__ __forceinline__ BcFun bc_functions(double l1, double l2, double D, double y) {
+  double E1m = (double)expf((float)(-l1 * (1.0 - y)));
+  double E1p = exp(-l1 * (1.0 + y));
+  double E2m = (double)expf((float)(-l2 * (1.0 - y)));
+  double E2p = exp(-l2 * (1.0 + y));
+  double p1 = 1.0 + exp(-l1 * 2.0), m1 = 1.0 - exp(-l1 * 2.0);
+  double p2 = 1.0 + exp(-l2 * 2.0), m2 = 1.0 - exp(-l2 * 2.0);
+  BcFun r;
+  r.v1 = 0.5 * D * ((E1m + E1p) / p1 - (E1m - E1p) / m1);
+  r.v1 += 0.5 * D * (-(E2m + E1p) / p2 + (E2m - E2p) / m2);
+  r.v2 = 0.5 * D * ((E1m + E1p) / p1 + (E1m - E1p) / m1);
+  r.v2 += 0.5 * D * (-(E2m + E1p) / p2 - (E2m - E2p) / m2);
+  r.dv1 = 0.5 * D * l1 * ((E1m - E1p) / p1 - (E1m + E1p) / m1);
+  r.dv1 += 0.5 * D * l2 * (-(E2m - E1p) / p2 + (E2m + E2p) / m2);
+  r.dv2 = 0.5 * D * l1 * ((E1m - E1p) / p1 + (E1m + E1p) / m1);
+  r.dv2 += 0.5 * D * l2 * (-(E2m - E1p) / p2 - (E2m + E2p) / m2);
+  r.ddv1 = 0.5 * ((E1m + E1p) / p1 - (E1m - E1p) / m1);
+  r.ddv2 = 0.5 * ((E1m + E1p) / p1 + (E1m - E1p) / m1);
+  return r;
+}
+
+// phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
+template <typename T>
+__device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
+                           T* phi, T* v, T* dv, double dvm, double dvp) {
+  const long st = 2 * a.M; const int ny = a.ny;
+  if (!((double)dt > 1e-8)) return;                       // bilplacSolver_double.cu:314 (Q6)
+  if (md.zero_mode) {                                     // :252-262
+    for (int j = 0; j < ny; j++) { long i = (long)j * st + md.e; phi[i] = 0; v[i] = 0; dv[i] = 0; }
+    return;
+  }
+  double l1 = sqrt(wv.kkd + a.reD / ((double)dt * (double)betha));
+  double l2 = sqrt(wv.kkd);
+  double D = 1.0 / (l1 * l1 - l2 * l2);
+  BcFun p = bc_functions(l1, l2, D, 1.0), q = bc_functions(l1, l2, D, -1.0);
+  double det = q.dv1 * p.dv2 - p.dv1 * q.dv2;
+  double c1 = p.dv2 * dvm - q.dv2 * dvp; c1 = -c1 / det;
+  double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
+  for (int j = 0; j < ny; j++) {
+    BcFun f = bc_functions(l1, l2, D, __ldg(a.yt.y + j));
+    long i = (long)j * st + md.e;
+    double pp = (double)phi[i], vv = (double)v[i], dd = (double)dv[i];
+    pp = pp + c1 * f.ddv1 + c2 * f.ddv2;
+    dd = dd + c1 * f.dv1 + c2 * f.dv2;
+    vv = vv + c1 * f.v1 + c2 * f.v2;
+    phi[i] = (T)pp; v[i] = (T)vv; dv[i] = (T)dd;
+  }
+}
+
+// ---- pointwise pieces ----------------------------------------------------------
+// own component of u, w from complex dv, g (calcUWkernel, nonLinear_kernels.cu:53-82)
+template <typename T, typename T2>
+__device__ __forceinline__ void uw_comp(const Wave<T>& wv, const Mode& md, bool zero_mode, const T2& dvz, const T2& gz, int c,
+                                        T& u, T& w) {
+  T kk = zero_mode ? (T)1 : wv.kk;
+  T s = c ? (T)1 : (T)-1;
+  T dp = other<T2, T>(dvz, c), gp = other<T2, T>(gz, c);
+  // u = i (k1 dv - k3 g)/kk ; w = i (k3 dv + k1 g)/kk, written in the reference's operation order
+  u = s * (wv.k1 * dp - wv.k3 * gp) / kk;
+  w = s * (wv.k3 * dp + wv.k1 * gp) / kk;
+  if (zero_mode) { u = 0; w = 0; }
+}
+
+// =================================================================================
+// pencil_pre: (dv, g, v, <u>) -> u, w, omega_x, omega_y, omega_z
+// =================================================================================
+template <typename T>
+__global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
+  typedef typename Vec2<T>::type T2;
+  Mode md; Wave<T> wv;
+  if (!setup(a, md, wv)) return;
+  const long st = 2 * a.M; const int ny = a.ny; const int c = md.c;
+  const bool with_mean = md.zero_mode && a.use_mean;
+  // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w
+  {
+    ElimD1 eu, ew;
+    for (int j = 0; j < ny; j++) {
+      long cm = (long)j * a.M + md.m;
+      T u, w;
+      if (a.op == OP_OMEGA) { u = ((const T*)a.u)[(long)j * st + md.e]; w = ((const T*)a.w)[(long)j * st + md.e]; }
+      else {
+        uw_comp<T, T2>(wv, md, md.zero_mode, a.dv[cm], a.g[cm], c, u, w);
+        if (with_mean) u = c ? (T)0 : a.mean_u[j];                 // writeUmean (nonLinear.c:19-21)
+      }
+      eu.step(a.yt.d1[0], 0, j, ny, (double)u, a.sA, st, md.e);
+      ew.step(a.yt.d1[0], 0, j, ny, (double)w, a.sB, st, md.e);
+    }
+  }
+  // pass 2 (down): back-substitute, build omega (calcOmegakernel, convolution_kernels.cu:46-53)
+  {
+    double xu = 0.0, xw = 0.0;
+    for (int j = ny - 1; j >= 0; j--) {
+      long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
+      double cp = __ldg(a.yt.d1[0].cp + j);
+      xu = a.sA[re] - cp * xu; xw = a.sB[re] - cp * xw;
+      T dudy = (T)xu, dwdy = (T)xw;
+      T u, w, up, wp;
+      if (a.op == OP_OMEGA) {
+        T2 uz = a.u[cm], wz = a.w[cm];
+        u = own<T2, T>(uz, c); up = other<T2, T>(uz, c); w = own<T2, T>(wz, c); wp = other<T2, T>(wz, c);
+      } else {
+        T2 dvz = a.dv[cm], gz = a.g[cm];
+        uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, c, u, w);
+        uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, c ^ 1, up, wp);
+        if (with_mean) { u = c ? (T)0 : a.mean_u[j]; up = c ? a.mean_u[j] : (T)0; }
+      }
+      T vp = other<T2, T>(a.v[cm], c);
+      T s = wv.sc;
+      T o1 = dwdy - s * wv.k3 * vp;                    // omega_x = dw/dy - i k3 v
+      T o2 = s * (wv.k3 * up - wv.k1 * wp);            // omega_y = i (k3 u - k1 w)
+      T o3 = -dudy + s * wv.k1 * vp;                   // omega_z = -du/dy + i k1 v
+      if (a.op != OP_OMEGA) { ((T*)a.u)[re] = u; ((T*)a.w)[re] = w; }
+      ((T*)a.ox)[re] = o1; ((T*)a.oy)[re] = o2; ((T*)a.oz)[re] = o3;
+      if (md.zero_mode && c == 0 && a.sc) {            // readUtau (convolution.c:14-16)
+        if (j == 0) a.sc->dudy_wall[0] = (double)dudy;
+        if (j == ny - 1) a.sc->dudy_wall[1] = (double)dudy;
+      }
+    }
+  }
+}
+
+// =================================================================================
+// pencil_post: H1..3, phi, g, R_phi, R_g -> phi, g, v, dv, R_phi, R_g   (7 passes)
+// =================================================================================
+template <typename T>
+__global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
+  typedef typename Vec2<T>::type T2;
+  Mode md; Wave<T> wv;
+  if (!setup(a, md, wv)) return;
+  const long st = 2 * a.M; const int ny = a.ny; const int c = md.c; const long e = md.e;
+  const T dt = (T)a.sc->dt;
+  const T s = wv.sc;
+  const T* phiR = (const T*)a.phi; const T* gR = (const T*)a.g;
+  const T2* H1 = a.ox; const T2* H3 = a.oz; const T* H2R = (const T*)a.oy;
+  // P1 (up): eliminate d/dy of phi, g and hv = -i (k1 H1 + k3 H3)  (calcHvgkernel, nonLinear_kernels.cu:129-130)
+  {
+    ElimD1 ep, eg, eh;
+    for (int j = 0; j < ny; j++) {
+      long cm = (long)j * a.M + md.m, re = (long)j * st + e;
+      T h1p = other<T2, T>(H1[cm], c), h3p = other<T2, T>(H3[cm], c);
+      T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
+      ep.step(a.yt.d1[0], 0, j, ny, (double)phiR[re], a.sA, st, e);
+      eg.step(a.yt.d1[0], 0, j, ny, (double)gR[re], a.sB, st, e);
+      eh.step(a.yt.d1[0], 0, j, ny, (double)hv, a.sC, st, e);
+    }
+  }
+  // P2 (down): phi', g', hv' ; eliminate d/dy of phi', g' (second derivative = d/dy twice, Q4)
+  {
+    ElimD1 ep, eg;
+    double xp = 0.0, xg = 0.0, xh = 0.0;
+    for (int jj = 0; jj < ny; jj++) {
+      int j = ny - 1 - jj; long re = (long)j * st + e;
+      double cp = __ldg(a.yt.d1[0].cp + j);
+      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg; xh = a.sC[re] - cp * xh;
+      a.sC[re] = rnd<T>(xh);
+      ep.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xp), a.sA, st, e);
+      eg.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xg), a.sB, st, e);
+    }
+  }
+  // P3 (up): phi'', g'' -> explicit RK update (rk_step_1/2, RK3_kernels.cu:76-80,138-142) -> eliminate implicit solves
+  const double bdt = (double)(dt * a.betha);                         // dt*betha in the state type (:235)
+  const double Dimp = a.nuD * bdt;
+  {
+    ElimVar<2> ev;
+    double* const ss[2] = { a.sA, a.sB };
+    double xp = 0.0, xg = 0.0;
+    for (int j = 0; j < ny; j++) {
+      long cm = (long)j * a.M + md.m, re = (long)j * st + e;
+      double cp = __ldg(a.yt.d1[1].cp + (ny - 1 - j));
+      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
+      T pyy = (T)xp, gyy = (T)xg;
+      T2 h1 = H1[cm], h3 = H3[cm];
+      T h1p = other<T2, T>(h1, c), h3p = other<T2, T>(h3, c);
+      T rp_new = (T)a.sC[re] - wv.kk * H2R[re];                       // calcHvvkernel (:180-181)
+      T rg_new = s * (wv.k3 * h1p - wv.k1 * h3p);                     // h_g = i (k3 H1 - k1 H3) (:132-133)
+      T p = phiR[re], g = gR[re];
+      T rp_old = ((const T*)a.Rphi)[re], rg_old = ((const T*)a.Rg)[re];
+      T pw = p + dt * (a.alpha * a.nuT * (pyy - wv.kk * p) + a.dseda * rp_old);
+      T gw = g + dt * (a.alpha * a.nuT * (gyy - wv.kk * g) + a.dseda * rg_old);
+      pw = pw + dt * a.gammad * rp_new;
+      gw = gw + dt * a.gammad * rg_new;
+      ((T*)a.Rphi)[re] = rp_new; ((T*)a.Rg)[re] = rg_new;
+      const double f[2] = { (double)pw, (double)gw };
+      ev.step(a.yt.d2[0], 0, j, ny, f, true, wv.kkd, Dimp, ss, st, e, a.sP, a.M, md.m);
+    }
+  }
+  // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new
+  {
+    ElimVar<1> eh;
+    double* const ss[1] = { a.sA };
+    double xp = 0.0, xg = 0.0;
+    for (int jj = 0; jj < ny; jj++) {
+      int j = ny - 1 - jj; long re = (long)j * st + e;
+      double cp = a.sP[(long)j * a.M + md.m];
+      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
+      // both components of a mode share the pivot row: every lane must have read row j before
+      // any lane overwrites it with the Helmholtz pivot of the lagging row (next iteration)
+      __syncwarp();
+      ((T*)a.g)[re] = (T)xg;
+      ((T*)a.phi)[re] = (T)xp;
+      const double f[1] = { rnd<T>(xp) };
+      eh.step(a.yt.d2[1], 1, jj, ny, f, false, wv.kkd, 0.0, ss, st, e, a.sP, a.M, md.m);
+    }
+  }
+  // P5 (up): v ; eliminate d/dy v
+  {
+    ElimD1 ev;
+    double xv = 0.0;
+    for (int j = 0; j < ny; j++) {
+      long re = (long)j * st + e;
+      xv = a.sA[re] - a.sP[(long)j * a.M + md.m] * xv;
+      ((T*)a.v)[re] = (T)xv;
+      ev.step(a.yt.d1[0], 0, j, ny, rnd<T>(xv), a.sA, st, e);
+    }
+  }
+  // P6 (down): dv
+  double dvm = 0.0, dvp = 0.0;
+  {
+    double x = 0.0;
+    for (int j = ny - 1; j >= 0; j--) {
+      long re = (long)j * st + e;
+      x = a.sA[re] - __ldg(a.yt.d1[0].cp + j) * x;
+      ((T*)a.dv)[re] = (T)x;
+      if (j == ny - 1) dvp = rnd<T>(x);
+      if (j == 0) dvm = rnd<T>(x);
+    }
+  }
+  // P7: wall correction (skipped when dt <= 1e-8, including the zeroing of mode (0,0))
+  bc_correct<T>(a, md, wv, a.betha, dt, (T*)a.phi, (T*)a.v, (T*)a.dv, dvm, dvp);
+}
+
+// =================================================================================
+// generic operator kernel (operator-level C ABI and the RKstep prologue)
+// =================================================================================
+template <typename T>
+__global__ void __launch_bounds__(128) op_kernel(PArgs<T> a) {
+  typedef typename Vec2<T>::type T2;
+  Mode md; Wave<T> wv;
+  if (!setup(a, md, wv)) return;
+  const long st = 2 * a.M; const int ny = a.ny; const int c = md.c;
+  T* f0 = (T*)a.f0; T* f1 = (T*)a.f1; T* f2 = (T*)a.f2;
+  switch (a.op) {
+    case OP_DERIV_Y: d1_solve<T>(a, md, f0, f0, a.sA); break;
+    case OP_DERIV_YY: d1_solve<T>(a, md, f0, f0, a.sA); d1_solve<T>(a, md, f0, f0, a.sA); break;
+    case OP_HELM: var_solve<T>(a, md, wv, false, 0.0, f0, f0, a.sA, a.sP); break;
+    case OP_IMPLICIT: {
+      double D = a.nuD * (double)(a.op_dt * a.op_betha);
+      var_solve<T>(a, md, wv, true, D, f0, f0, a.sA, a.sP);
+    } break;
+    case OP_VDV:           // calcVdV (RK3.c:52-62): f1 = Helmholtz(f0), f2 = d/dy f1
+      var_solve<T>(a, md, wv, false, 0.0, f0, f1, a.sA, a.sP);
+      d1_solve<T>(a, md, f1, f2, a.sA);
+      break;
+    case OP_BILAP: {       // bilaplaSolver_double (bilplacSolver_double.cu:320-348)
+      double D = a.nuD * (double)(a.op_dt * a.op_betha);
+      var_solve<T>(a, md, wv, true, D, f0, f0, a.sA, a.sP);
+      var_solve<T>(a, md, wv, false, 0.0, f0, f1, a.sA, a.sP);
+      d1_solve<T>(a, md, f1, f2, a.sA);
+      double dvm = (double)f2[md.e], dvp = (double)f2[(long)(ny - 1) * st + md.e];
+      bc_correct<T>(a, md, wv, a.op_betha, a.op_dt, f0, f1, f2, dvm, dvp);
+    } break;
+    case OP_UW:            // calcUW: (f0 = dv, f1 = g) -> (u, w)
+      for (int j = 0; j < ny; j++) {
+        long cm = (long)j * a.M + md.m; T u, w;
+        uw_comp<T, T2>(wv, md, md.zero_mode, a.f0[cm], a.f1[cm], c, u, w);
+        ((T*)a.u)[(long)j * st + md.e] = u; ((T*)a.w)[(long)j * st + md.e] = w;
+      }
+      break;
+    case OP_HVG: {         // calcHvg (nonLinear_kernels.cu:212-232): f0 = H1 -> h_v, f2 = H3 -> h_g, f1 = H2
+      T s = wv.sc;
+      T* tmp = (T*)a.u;    // work field
+      for (int j = 0; j < ny; j++) {
+        long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
+        T h1p = other<T2, T>(a.f0[cm], c), h3p = other<T2, T>(a.f2[cm], c);
+        tmp[re] = -s * (wv.k1 * h1p + wv.k3 * h3p);
+        ((T*)a.w)[re] = s * (wv.k3 * h1p - wv.k1 * h3p);
+      }
+      __syncwarp();   // partner components are read above before anything is overwritten below
+      d1_solve<T>(a, md, tmp, tmp, a.sA);
+      for (int j = 0; j < ny; j++) {
+        long re = (long)j * st + md.e;
+        f0[re] = tmp[re] - wv.kk * f1[re];
+        f2[re] = ((T*)a.w)[re];
+      }
+    } break;
+  }
+}
+
+// ---------------------------------------------------------------------------------
+template <typename T>
+static void fill_args(chan_handle* h, PArgs<T>& a) {
+  typedef typename Vec2<T>::type T2;
+  a.phi = (T2*)h->phi; a.g = (T2*)h->g; a.v = (T2*)h->v; a.dv = (T2*)h->dv; a.Rphi = (T2*)h->Rphi; a.Rg = (T2*)h->Rg;
+  a.u = (T2*)h->u; a.w = (T2*)h->w; a.ox = (T2*)h->ox; a.oy = (T2*)h->oy; a.oz = (T2*)h->oz;
+  a.sA = h->sA; a.sB = h->sB; a.sC = h->sC; a.sP = h->sP;
+  a.mean_u = (const T*)h->mean_u; a.sc = h->sc; a.yt = h->yt;
+  a.ny = h->d.ny; a.Kz = h->d.Kz; a.ikx0 = h->d.ikx0; a.kxmax = h->d.kxmax; a.Kx = h->d.Kx; a.M = h->d.M;
+  // channel.h:53-57: PI2 = 2.0f*3.14159265f, LX = 1.0f*PI2, LZ = 0.5f*PI2 (float arithmetic, widened for double)
+  const float PI2 = 2.0f * 3.14159265f, LX = 1.0f * PI2, LZ = 0.5f * PI2;
+  a.k1fac = (T)PI2 / (T)LX; a.k3fac = (T)PI2 / (T)LZ;
+  const float re = (float)h->cfg.reynolds;                 // const float REYNOLDS (channel.h:61)
+  a.nuT = (T)1.0f / (T)re;
+  a.nuD = 1.0 / (double)re;
+  a.reD = (double)re;
+  a.n = 0; a.alpha = a.dseda = a.gammad = a.betha = 0;
+  a.op = 0; a.f0 = a.f1 = a.f2 = 0; a.op_betha = 0; a.op_dt = 0; a.use_mean = 1;
+}
+
+static const float kAlpha[3] = { 29.0f / 96.0f, -3.0f / 40.0f, 1.0f / 6.0f };     // RK3_kernels.cu:24
+static const float kDseda[3] = { 0.0f, -17.0f / 60.0f, -5.0f / 12.0f };           // RK3_kernels.cu:25
+static const float kGamma[3] = { 8.0f / 15.0f, 5.0f / 12.0f, 3.0f / 4.0f };       // RK3_kernels.cu:113
+static const float kBetha[3] = { 37.0f / 160.0f, 5.0f / 24.0f, 1.0f / 6.0f };     // RK3.c:14
+
+template <typename T>
+static int pre_t(chan_handle* h) {
+  PArgs<T> a; fill_args<T>(h, a);
+  long nchain = 2 * h->d.M;
+  pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
+  h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+template <typename T>
+static int post_t(chan_handle* h, int n) {
+  PArgs<T> a; fill_args<T>(h, a);
+  a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
+  long nchain = 2 * h->d.M;
+  pencil_post_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
+  h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+template <typename T>
+static int op_t(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt) {
+  typedef typename Vec2<T>::type T2;
+  PArgs<T> a; fill_args<T>(h, a);
+  a.op = op; a.f0 = (T2*)f0; a.f1 = (T2*)f1; a.f2 = (T2*)f2; a.op_betha = (T)betha; a.op_dt = (T)dt;
+  long nchain = 2 * h->d.M;
+  unsigned grid = (unsigned)((nchain + 127) / 128);
+  if (op == OP_OMEGA) { a.use_mean = 0; pencil_pre_kernel<T><<<grid, 128, 0, h->stream>>>(a); }
+  else op_kernel<T><<<grid, 128, 0, h->stream>>>(a);
+  h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+
+int launch_pencil_pre(chan_handle* h) { return h->prec == 4 ? pre_t<float>(h) : pre_t<double>(h); }
+int launch_pencil_post(chan_handle* h, int n) { return h->prec == 4 ? post_t<float>(h, n) : post_t<double>(h, n); }
+int launch_op(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt) {
+  return h->prec == 4 ? op_t<float>(h, op, f0, f1, f2, betha, dt) : op_t<double>(h, op, f0, f1, f2, betha, dt);
+}
+
+}  // namespace chan

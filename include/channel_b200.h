@@ -1,0 +1,136 @@
+/* libchannel_b200 — C ABI of the B200-native KMM channel-flow RK3 time-stepper.
+ *
+ * Drop-in boundary for the hot path of Nasrollah/CHANNEL_GPU (one RK3 step of
+ * the (phi = lap v, g = omega_y) formulation).  The reference has no FFI layer:
+ * its seam is the set of free functions of src/channel.h that RK3.c,
+ * nonLinear.c, convolution.c and imposeSymetry.c call.  Each entry point below
+ * names the reference interface it replaces (file:line under
+ * /root/reference/src).  INTEGRATION.md shows the binding a maintainer adds.
+ *
+ * Conventions
+ *  - plain C, opaque handle, int return codes (0 = CHAN_OK); the reference's
+ *    print-and-exit(1) error helpers (check.cu:3-79) become codes plus
+ *    chan_last_error().
+ *  - "reference layout": complex array [NX][NZ][NY], index h = i*NY*NZ + k*NY + j
+ *    (RK3_kernels.cu:16-18), element type float2 (precision 4, the reference as
+ *    shipped) or double2 (precision 8), spectral coefficients un-normalised
+ *    (x N2 = NX*(2NZ-2), convolution_kernels.cu:93).  NZ counts COMPLEX z modes;
+ *    the physical z size is 2NZ-2 (fft.c:17).
+ *  - *_dev arguments are DEVICE pointers in the reference layout, updated in
+ *    place exactly like the reference functions they replace; inside, the
+ *    library keeps only the active modes of the 2/3 rule (dealias.cu:37) in its
+ *    own plane-major layout, so truncated modes come back as exact zeros.
+ *  - grid sizes are run-time values (the reference bakes -DNX -DNY -DNZ in at
+ *    compile time, Makefile:8-11, channel.h:42-44); NY is not limited to 1024
+ *    (main.c:79) and NX, NY need no divisibility (channel.h:72-73).
+ *  - one handle drives one GPU; no globals; calls on one handle are not
+ *    re-entrant (neither is the reference: static handles per translation unit).
+ */
+#ifndef CHANNEL_B200_H
+#define CHANNEL_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct chan_handle chan_handle;
+
+enum {
+  CHAN_OK = 0,
+  CHAN_ERR_ARG = 1,      /* bad argument / unsupported size                       */
+  CHAN_ERR_CUDA = 2,     /* a CUDA runtime call or kernel failed                  */
+  CHAN_ERR_ALLOC = 3,    /* out of device or host memory                          */
+  CHAN_ERR_STATE = 4     /* call order (e.g. step before fields were set)         */
+};
+
+/* Replaces domain_t (channel.h:23-30) and the compile-time constants of
+ * channel.h:50-62, RK3.c:68.  chan_config_default() fills the reference's values. */
+typedef struct chan_config {
+  int nx, ny, nz;        /* run.conf application.NX/NY/NZ (config.c:18-23)        */
+  int precision;         /* 4 = float state (as shipped), 8 = double state        */
+  double reynolds;       /* REYNOLDS   channel.h:61  (3250)                       */
+  double qvelocity;      /* QVELOCITY  channel.h:62  (1.8)                        */
+  double cfl;            /* CFL        RK3.c:68      (0.5)                        */
+  int rank, size;        /* domain_t.rank/size: slab of a multi-GPU run           */
+  int device;            /* CUDA device ordinal, -1 = current (main.c:87)         */
+  int plane_batch;       /* y-planes per FFT-stage launch group, 0 = auto         */
+} chan_config;
+
+typedef struct chan_scalars {
+  double dt, dt_next, dt_c, dt_v;     /* RK3.c:64-109, 114, 179                   */
+  double umax[3];                     /* max |u|,|v|,|w| (un-normalised) fft.c:143 */
+  double utau[2];                     /* meanUevol.c:178-199                      */
+  int counter;                        /* steps taken (RK3.c:180)                  */
+} chan_scalars;
+
+/* field selectors for chan_get_field / chan_set_field (globals of RK3.c:4-12) */
+enum { CHAN_F_DDV = 0, CHAN_F_G, CHAN_F_V, CHAN_F_DV, CHAN_F_R_DDV, CHAN_F_R_G,
+       CHAN_F_U, CHAN_F_W, CHAN_F_WX, CHAN_F_WY, CHAN_F_WZ, CHAN_F_COUNT };
+
+int  chan_config_default(chan_config* cfg);
+/* setUp (setUp.c:3-29) + setRK3 (RK3.c:17-50) + setRKmean (meanUevol.c:43-84) */
+int  chan_create(const chan_config* cfg, chan_handle** out);
+void chan_destroy(chan_handle* h);
+const char* chan_last_error(const chan_handle* h);
+long chan_launch_count(const chan_handle* h);   /* kernels launched so far */
+
+/* ---- state in/out, HOST pointers, reference layout ------------------------- */
+/* readData / genRandData + cudaMemcpy H2D (io.c:3-34,74-98; main.c:107-114) */
+int chan_set_fields(chan_handle* h, const void* ddv_host, const void* g_host);
+/* cudaMemcpy D2H + writeData (io.c:37-72) */
+int chan_get_fields(chan_handle* h, void* ddv_host, void* g_host);
+int chan_get_field(chan_handle* h, int which, void* host);
+int chan_set_field(chan_handle* h, int which, const void* host);
+/* readU / writeU payload (meanUevol.c:153-176): NY complex, .x = <u>(y)*N2 */
+int chan_set_umean(chan_handle* h, const void* umean_host);
+int chan_get_umean(chan_handle* h, void* umean_host);
+/* N_host of meanUevol.c:127-133: NY reals (double) */
+int chan_get_nmean(chan_handle* h, double* out_ny);
+int chan_get_scalars(chan_handle* h, chan_scalars* out);
+/* >0: use this dt for every following step instead of calcDt (test/bench hook) */
+int chan_set_fixed_dt(chan_handle* h, double dt);
+/* dt of the step about to run (the reference starts with 0, RK3.c:114) */
+int chan_set_dt(chan_handle* h, double dt);
+
+/* ---- the hot path ---------------------------------------------------------- */
+/* RKstep prologue (RK3.c:120-123): dealias, imposeSymetry, calcVdV */
+int chan_rk_init(chan_handle* h);
+/* body of RKstep's while loop (RK3.c:127-191), nsteps times, asynchronous */
+int chan_rk_step(chan_handle* h, int nsteps);
+/* one pass of the n_step loop (RK3.c:129-167), n = 0,1,2 */
+int chan_rk_substep(chan_handle* h, int n);
+/* RK3.c:174-179 (symmetry cadence, dt lag, counter) */
+int chan_rk_end_step(chan_handle* h);
+int chan_sync(chan_handle* h);
+/* calcSt + sumElementsComplex (statistics.cu:161-243, fft.c:239-269): the four
+ * per-plane sums (Reynolds stress, u, v, w) before the sqrt of the printout */
+int chan_statistics(chan_handle* h, double* out_4ny_host);
+
+/* ---- operator level, DEVICE pointers, reference layout, in place ------------ */
+int chan_dealias(chan_handle* h, void* u_dev);                                  /* dealias            channel.h:243 */
+int chan_deriv_y(chan_handle* h, void* u_dev);                                  /* deriv_Y_HO_double  channel.h:239 */
+int chan_deriv_yy(chan_handle* h, void* u_dev);                                 /* deriv_YY_HO_double channel.h:240 */
+int chan_helmholtz(chan_handle* h, void* u_dev);                                /* hemholztSolver_double channel.h:212 */
+int chan_implicit(chan_handle* h, void* u_dev, double betha, double dt);        /* implicitSolver_double channel.h:230 */
+int chan_bilaplacian(chan_handle* h, void* ddv_dev, void* v_dev, void* dv_dev,
+                     double betha, double dt);                                  /* bilaplaSolver_double  channel.h:265 */
+int chan_calc_uw(chan_handle* h, void* ux_dev, void* uz_dev,
+                 const void* f_dev, const void* g_dev);                         /* calcUW             channel.h:221 */
+int chan_convolution(chan_handle* h, void* ux_dev, void* uy_dev, void* uz_dev,
+                     void* wx_dev, void* wy_dev, void* wz_dev);                 /* convolution        channel.h:179 */
+int chan_calc_hvg(chan_handle* h, void* nlx_dev, void* nly_dev, void* nlz_dev); /* calcHvg            channel.h:222 */
+int chan_impose_symmetry(chan_handle* h, void* u_dev, void* v_dev);             /* imposeSymetry      channel.h:175 */
+/* fftBackwardTranspose (channel.h:116): spectral [NX][NZ][NY] -> real planes
+ * [NY][NX][2NZ] (2NZ-2 points + 2 pad floats per row, fft.c:17-21), out of place */
+int chan_fft_backward_transpose(chan_handle* h, const void* u_dev, void* phys_dev);
+
+/* ---- slab decomposition (main.c:47, channel.h:71-79), pure host arithmetic --- */
+/* splits n items over `size` ranks as evenly as possible: [*start, *start+*count) */
+int chan_partition(int n, int size, int rank, int* start, int* count);
+int chan_active_kx(int nx);     /* 2*floor(nx/3)+1 */
+int chan_active_kz(int nz);     /* floor((2nz-2)/3)+1 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
