@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py — RK3 steps/s of the KMM channel-flow time-stepper on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--config re180|re550|re1000] [--precision 8|4]
+
+One "step" is one full RK3 step (three substeps) of the named grid from a
+synthetic, self-generated field (seeded smooth random modes on a laminar mean
+profile; run time does not depend on the data for a given dt).  Prints ONE JSON
+line.  Workload at N=1: BASELINE.json configs[1], Re_tau=550, 384x193x384
+physical (NX x NY x NZ = 384x193x193), fp64 state.
+
+value      whole-job RK3 steps/s, state resident in HBM, timed on the device with
+           CUDA events on the library's stream (chan_get_stage_ms stage 4).
+e2e        the same through the public call a user makes (Channel.RKstep-like:
+           pinned host fields -> H2D -> rk_init -> K steps, each followed by a D2H
+           read of the step scalars -> D2H of the fields), wall clock.
+roofline   dominant kernel (pencil_post: the fused y-stage) against the measured
+           HBM copy peak of MEASURED_PEAKS.json.
+cpu_baseline  oracle/kmm.py (numpy port) on a bounded sample of the same workload.
+--impl reference  times oracle/_ref/ref_<grid>_f64, the reference's own CUDA
+           sources built by oracle/build_ref.sh (the reference has no CPU path).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    "re180": dict(nx=128, ny=97, nz=65, name="Re_tau=180 channel, 128x97x128"),
+    "re550": dict(nx=384, ny=193, nz=193, name="Re_tau=550 channel, 384x193x384"),
+    "re1000": dict(nx=1024, ny=385, nz=385, name="Re_tau=1000 channel, 1024x385x768"),
+}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def sizes(cfg, prec):
+    nx, ny, nz = cfg["nx"], cfg["ny"], cfg["nz"]
+    Kx, Kz = 2 * (nx // 3) + 1, (2 * nz - 2) // 3 + 1
+    c = 2 * prec
+    n_act = Kx * Kz * ny
+    return dict(Kx=Kx, Kz=Kz, n_act=n_act, P=n_act * c, Qc=nx * Kz * ny * c, mpts=nx * ny * (2 * nz - 2) / 1e6)
+
+
+def synthetic_fields(nx, ny, nz, cplx, amp=0.12, seed=20261106):
+    """Smooth random (phi, g) on the active modes + laminar mean (simplified)."""
+    from oracle.kmm import Grid  # mesh only (test infrastructure used as a data generator)
+    rng = np.random.default_rng(seed)
+    y = Grid(nx, ny, nz).coef()["y"]
+    n2 = nx * (2 * nz - 2)
+    i = np.arange(nx); kx = np.where(i < nx // 2, i, i - nx).astype(np.float64); kz = np.arange(nz, dtype=np.float64)
+    a = np.exp(-(kx[:, None] / (nx / 9.0)) ** 2 - (kz[None, :] / ((2 * nz - 2) / 9.0)) ** 2)
+    a[(np.abs(kx)[:, None] > nx // 3) | (kz[None, :] > (2 * nz - 2) // 3)] = 0
+    shapes = np.stack([1 - y ** 2, y * (1 - y ** 2), (1 - y ** 2) ** 2])
+
+    def field(scale):
+        out = np.empty((nx, nz, ny), cplx)
+        for s0 in range(0, nx, 32):          # chunked to bound host memory
+            s1 = min(nx, s0 + 32)
+            xi = rng.standard_normal((s1 - s0, nz, 3)) + 1j * rng.standard_normal((s1 - s0, nz, 3))
+            out[s0:s1] = np.einsum("xzs,sj->xzj", xi, shapes) * a[s0:s1, :, None] * (scale * n2)
+        return out
+
+    return field(amp * 6.0), field(amp * 2.0), (1.35 * (1 - y ** 2) * n2).astype(cplx)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu=0):
+        self.lines = []; self.p = None; self.gpu = gpu
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._rd, daemon=True); self.t.start()
+        except Exception:
+            self.p = None
+
+    def _rd(self):
+        for l in self.p.stdout:
+            self.lines.append(l.strip())
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline_sample(cfg, prec):
+    """oracle/kmm.py on a bounded sample of the workload: the pencil work of one substep on a
+    1/16 kx slab and the plane work on 8 y-planes, each scaled to the full grid."""
+    from oracle import kmm
+    nx, ny, nz = cfg["nx"], cfg["ny"], cfg["nz"]
+    real = np.float64 if prec == 8 else np.float32
+    nxl = max(8, nx // 16); nyl = 8
+    Gs = kmm.Grid(nx, ny, nz, real, i_range=(0, nxl)); Gf = kmm.Grid(nx, ny, nz, real)
+    rng = np.random.default_rng(1)
+    mk = lambda s: (rng.standard_normal(s) + 1j * rng.standard_normal(s)).astype(Gs.cplx)
+    f = [mk((nxl, nz, ny)) for _ in range(6)]
+    dt = 1e-3; n = 1
+    t0 = time.perf_counter()
+    pw = kmm.rk_step_1(Gs, f[0], kmm.deriv_yy(Gs, f[0]), f[2], dt, n)
+    gw = kmm.rk_step_1(Gs, f[1], kmm.deriv_yy(Gs, f[1]), f[3], dt, n)
+    u, w = kmm.calc_uw(Gs, f[4], f[1])
+    wz = kmm.deriv_y(Gs, u); wx = kmm.deriv_y(Gs, w)
+    kmm.calc_omega(Gs, wx, wz, u, f[5], w)
+    hv, hg = kmm.calc_hvg(Gs, f[2], f[3], f[4])
+    pw = kmm.rk_step_2(Gs, pw, hv, dt, n); gw = kmm.rk_step_2(Gs, gw, hg, dt, n)
+    kmm.implicit(Gs, gw, kmm.BETHA[n], dt)
+    kmm.bilaplacian(Gs, pw, kmm.BETHA[n], dt)
+    t_pen = (time.perf_counter() - t0) * nx / nxl
+    p = [mk((nx, nz, nyl)) for _ in range(6)]
+    t0 = time.perf_counter()
+    ph = [kmm.to_physical(Gf, a) for a in p]
+    m = kmm.rotor(Gf, *ph)
+    for a in m:
+        kmm.dealias(Gf, kmm.to_spectral(Gf, a))
+    t_pl = (time.perf_counter() - t0) * ny / nyl
+    step = 3.0 * (t_pen + t_pl)
+    return {"value": 1.0 / step, "unit": "steps/s", "cores": 1, "kind": "port",
+            "sample": "oracle/kmm.py (numpy): pencil work of one substep on a %d/%d kx slab + plane work on %d/%d planes, scaled to the grid, x3 substeps" % (nxl, nx, nyl, ny)}
+
+
+def run_reference(args, cfg):
+    """The reference's own sources (oracle/_ref, built by oracle/build_ref.sh) on the same grid."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    prec = 64 if args.precision == 8 else 32
+    b = os.path.join(ROOT, "oracle", "_ref", "ref_%dx%dx%d_f%d" % (cfg["nx"], cfg["ny"], cfg["nz"], prec))
+    base = {"impl": "reference", "metric": "RK3 steps/s", "unit": "steps/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if args.precision == 8 else "f32",
+            "data": "the reference's own initial field (io.c:76-94)"}
+    if not os.path.exists(b):
+        base.update({"unavailable": "reference binary %s not built (oracle/build_ref.sh needs /root/reference)" % os.path.basename(b)})
+        print(json.dumps(base)); return
+    r = subprocess.run([b, "time", str(args.steps), str(args.warmup)], capture_output=True, text=True, timeout=3000)
+    line = [l for l in r.stderr.splitlines() if l.startswith("REF_TIME")]
+    if not line:
+        base.update({"unavailable": "reference run failed: " + (r.stderr[-200:] or r.stdout[-200:]).replace("\n", " ")})
+        print(json.dumps(base)); return
+    ms = float(line[0].split("ms_per_step=")[1])
+    v = 1e3 / ms
+    sz = sizes(cfg, args.precision)
+    base.update({"value": v, "ms_per_step": ms, "mpts_step_per_s": v * sz["mpts"],
+                 "config": {"workload": cfg["name"] + ", fp64 state, 1 GPU" if args.precision == 8 else cfg["name"] + ", fp32 state, 1 GPU",
+                            "grid": [cfg["nx"], cfg["ny"], cfg["nz"]], "note": "reference CUDA build (cuFFT/cuSPARSE/cuBLAS, host-staged transposes), single rank on one GPU whatever --gpus says: its slab code needs NY%size==0 (channel.h:72-73) and no MPI exists on the box"},
+                 "cpu_baseline": {"value": v, "unit": "steps/s", "cores": 1, "kind": "reference",
+                                  "sample": "full workload; the reference has no CPU implementation, this is its CUDA build driven by one host thread"},
+                 "e2e": {"value": v, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    print(json.dumps(base))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", default="re550")
+    ap.add_argument("--precision", type=int, default=8)
+    ap.add_argument("--plane-batch", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="device-timed leg only (for ncu runs)")
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    if args.impl == "reference":
+        return run_reference(args, cfg)
+
+    import torch
+    import channel_gpu_b200 as cg
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    W = max(3, args.warmup); K = args.steps
+    nx, ny, nz = cfg["nx"], cfg["ny"], cfg["nz"]
+    prec = args.precision
+    cplx = np.complex128 if prec == 8 else np.complex64
+    sz = sizes(cfg, prec)
+
+    if world > 1:
+        raise SystemExit("multi-GPU bench not wired yet")
+
+    ddv, g, um = synthetic_fields(nx, ny, nz, cplx)
+    # pinned host staging for the end-to-end leg
+    def pinned(a):
+        t = torch.from_numpy(a).pin_memory()
+        return t, t.numpy()
+    ddv_t, ddv_p = pinned(ddv); g_t, g_p = pinned(g)
+    out_ddv_t = torch.empty_like(ddv_t).pin_memory(); out_g_t = torch.empty_like(g_t).pin_memory()
+
+    ch = cg.Channel(nx, ny, nz, precision=prec, device=local, plane_batch=args.plane_batch)
+    ch.set_fields(ddv_p, g_p); ch.set_umean(um)
+    ch.rk_init()
+    ch.rk_step(W); ch.sync()
+
+    # ---- device-resident timing --------------------------------------------------------
+    clocks = ClockSampler(local); clocks.start()
+    ch.set_timing(True); ch.stage_ms()
+    l0 = ch.launch_count()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ch.rk_step(K)
+    ch.sync()
+    wall = time.perf_counter() - t0
+    ms, cnt = ch.stage_ms()
+    launches = ch.launch_count() - l0
+    ch.set_timing(False)
+    clk = clocks.stop()
+    step_ms = ms[4] / max(cnt[4], 1)
+    value = 1e3 / step_ms
+    sc = ch.scalars()
+    finite = bool(np.isfinite(sc["dt_next"]) and np.isfinite(sc["umax"][0]))
+
+    # ---- end to end through the public API with host buffers ----------------------------
+    if args.profile:
+        print(json.dumps({"profile_run": True, "ms_per_step": step_ms, "stage_ms": ms, "launches": launches}))
+        return
+    ch2 = ch
+    t0 = time.perf_counter()
+    ch2.set_fields(ddv_p, g_p); ch2.set_umean(um)
+    ch2.rk_init()
+    d2h_scalars = 0
+    for _ in range(K):
+        ch2.rk_step(1)
+        s = ch2.scalars(); d2h_scalars += 96
+    o1, o2 = ch2.get_fields()
+    e2e_s = time.perf_counter() - t0
+    fb = ddv.nbytes
+    e2e = {"value": K / e2e_s, "unit": "steps/s", "h2d_bytes_per_step": int(2 * fb / K), "d2h_bytes_per_step": int((2 * fb + d2h_scalars) / K),
+           "note": "set_fields (pinned H2D + relayout) + rk_init + K x (rk_step + D2H scalars) + get_fields (relayout + D2H); field copies amortised over K steps"}
+
+    # ---- roofline of the dominant kernel ---------------------------------------------------
+    peak, peak_src = measured_peaks()
+    P = sz["P"]; Qc = sz["Qc"]
+    stage_bytes = {"pencil_pre": 9 * P, "planes": 6 * P + 6 * Qc + 6 * Qc + 3 * Qc + 3 * Qc + 3 * P, "pencil_post": 13 * P}
+    stage_ms = {"pencil_pre": ms[0] / max(cnt[0], 1), "planes": ms[1] / max(cnt[1], 1), "scalar": ms[2] / max(cnt[2], 1), "pencil_post": ms[3] / max(cnt[3], 1)}
+    stages = {k: {"ms": stage_ms[k], "alg_GB": stage_bytes[k] / 1e9, "GBps": stage_bytes[k] / 1e6 / stage_ms[k]} for k in stage_bytes}
+    stages["scalar"] = {"ms": stage_ms["scalar"]}
+    dom = max(stage_bytes, key=lambda k: stage_ms[k])
+    traffic = None
+    pj = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    if os.path.exists(pj):
+        traffic = json.load(open(pj)).get(dom, {}).get("dram_bytes_per_launch")
+    ach = stage_bytes[dom] / 1e6 / stage_ms[dom]
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+                "peak_source": peak_src, "alg_bytes_per_launch": stage_bytes[dom],
+                "step_frac": (3 * (31 * P + 18 * Qc) / 1e6 / step_ms) / peak}
+
+    out = {"metric": "RK3 steps/s", "value": value, "unit": "steps/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms,
+           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if prec == 8 else "f32",
+           "data": "synthetic (seeded smooth random modes on a laminar mean profile, free-running CFL dt)",
+           "mpts_step_per_s": value * sz["mpts"],
+           "config": {"workload": cfg["name"] + (", fp64 state" if prec == 8 else ", fp32 state") + ", %d GPU" % world,
+                      "grid": [nx, ny, nz], "active_modes": sz["n_act"], "plane_batch_arg": args.plane_batch,
+                      "l2": "working set per step (>1 GB) exceeds the 126 MB L2; no flush needed", "finite": finite},
+           "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "stages": stages,
+           "wall_ms_per_step": 1e3 * wall / K}
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline_sample(cfg, prec)
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -57,6 +57,7 @@ def load_library():
         "chan_set_fixed_dt": [vp, cd], "chan_set_dt": [vp, cd],
         "chan_rk_init": [vp], "chan_rk_step": [vp, ci], "chan_rk_substep": [vp, ci], "chan_rk_end_step": [vp],
         "chan_sync": [vp], "chan_statistics": [vp, vp],
+        "chan_set_timing": [vp, ci], "chan_get_stage_ms": [vp, C.POINTER(cd), C.POINTER(C.c_long)],
         "chan_dealias": [vp, vp], "chan_deriv_y": [vp, vp], "chan_deriv_yy": [vp, vp], "chan_helmholtz": [vp, vp],
         "chan_implicit": [vp, vp, cd, cd], "chan_bilaplacian": [vp, vp, vp, vp, cd, cd],
         "chan_calc_uw": [vp, vp, vp, vp, vp], "chan_convolution": [vp, vp, vp, vp, vp, vp, vp],
@@ -199,6 +200,15 @@ class Channel:
 
     def sync(self):
         self._ck(self.L.chan_sync(self.h), "chan_sync")
+
+    def set_timing(self, on=True):
+        self._ck(self.L.chan_set_timing(self.h, int(bool(on))), "chan_set_timing")
+
+    def stage_ms(self):
+        """Accumulated device milliseconds and counts per stage (pre, planes, scalar, post, whole step) since the last call."""
+        ms = (C.c_double * 5)(); cnt = (C.c_long * 5)()
+        self._ck(self.L.chan_get_stage_ms(self.h, ms, cnt), "chan_get_stage_ms")
+        return list(ms), list(cnt)
 
     def launch_count(self):
         return int(self.L.chan_launch_count(self.h))

@@ -97,6 +97,7 @@ extern "C" void chan_destroy(chan_handle* h) {
                    h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
+  for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -198,13 +199,43 @@ extern "C" int chan_rk_init(chan_handle* h) {
   return launch_op(h, OP_VDV, h->phi, h->v, h->dv, 0.0, 0.0);
 }
 
+// ---- optional stage timing ----------------------------------------------------------
+static int t_begin(chan_handle* h, int stage) {
+  if (!h->timing || h->n_ev >= 1024) return -1;
+  int i = h->n_ev++;
+  if (!h->ev0[i]) { cudaEventCreate(&h->ev0[i]); cudaEventCreate(&h->ev1[i]); }
+  h->ev_stage[i] = stage;
+  cudaEventRecord(h->ev0[i], h->stream);
+  return i;
+}
+static void t_end(chan_handle* h, int i) { if (i >= 0) cudaEventRecord(h->ev1[i], h->stream); }
+
+extern "C" int chan_set_timing(chan_handle* h, int on) { if (!h) return CHAN_ERR_ARG; h->timing = on; return CHAN_OK; }
+extern "C" int chan_get_stage_ms(chan_handle* h, double* ms, long* cnt) {
+  if (!h || !ms || !cnt) return CHAN_ERR_ARG;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int s = 0; s < CHAN_STAGE_COUNT; s++) { ms[s] = 0; cnt[s] = 0; }
+  for (int i = 0; i < h->n_ev; i++) {
+    float t = 0; CHAN_CUDA(h, cudaEventElapsedTime(&t, h->ev0[i], h->ev1[i]));
+    ms[h->ev_stage[i]] += t; cnt[h->ev_stage[i]]++;
+  }
+  h->n_ev = 0;
+  return CHAN_OK;
+}
+
 extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if (!h || n < 0 || n > 2) return CHAN_ERR_ARG;
-  int rc;
+  int rc, t;
+  t = t_begin(h, CHAN_STAGE_PRE);
   if ((rc = launch_pencil_pre(h))) return rc;            // calcUW + writeUmean + d/dy + calcOmega
+  t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
+  t_end(h, t); t = t_begin(h, CHAN_STAGE_SCALAR);
   if ((rc = launch_scalar_stage(h, n))) return rc;        // mean flow, calcDt
-  return launch_pencil_post(h, n);                        // RK explicit + h_v,h_g + implicit + bi-Laplacian
+  t_end(h, t); t = t_begin(h, CHAN_STAGE_POST);
+  rc = launch_pencil_post(h, n);                          // RK explicit + h_v,h_g + implicit + bi-Laplacian
+  t_end(h, t);
+  return rc;
 }
 
 extern "C" int chan_rk_end_step(chan_handle* h) {
@@ -218,8 +249,10 @@ extern "C" int chan_rk_end_step(chan_handle* h) {
 extern "C" int chan_rk_step(chan_handle* h, int nsteps) {
   if (!h || nsteps < 0) return CHAN_ERR_ARG;
   for (int s = 0; s < nsteps; s++) {
+    int t = t_begin(h, CHAN_STAGE_STEP);
     for (int n = 0; n < 3; n++) { int rc = chan_rk_substep(h, n); if (rc) return rc; }
     int rc = chan_rk_end_step(h); if (rc) return rc;
+    t_end(h, t);
   }
   return CHAN_OK;
 }

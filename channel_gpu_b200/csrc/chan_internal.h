@@ -97,6 +97,8 @@ struct chan_handle {
   void* io_buf; size_t io_bytes;
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
+  // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
+  int timing; int n_ev; cudaEvent_t ev0[1024], ev1[1024]; int ev_stage[1024];
   char err[256];
 };
 

@@ -43,7 +43,7 @@ DSEDA = [F32(0.0), F32(-17.0) / F32(60.0), F32(-5.0) / F32(12.0)]
 class Grid:
     """channel.h:42-62 constants for one grid and state type."""
 
-    def __init__(self, nx, ny, nz, real=np.float64, reynolds=3250.0, qvelocity=1.8):
+    def __init__(self, nx, ny, nz, real=np.float64, reynolds=3250.0, qvelocity=1.8, i_range=None):
         self.nx, self.ny, self.nz = int(nx), int(ny), int(nz)
         self.real = np.dtype(real).type
         self.cplx = np.complex64 if self.real is F32 else np.complex128
@@ -57,7 +57,9 @@ class Grid:
         self.LZ = R(F32(0.5)) * self.PI2                 # channel.h:57
         self.REYNOLDS = R(F32(reynolds))                 # channel.h:61
         self.QVELOCITY = R(F32(qvelocity))               # channel.h:62
-        i = np.arange(self.nx)
+        # i_range = (i0, i1): this object describes the kx slab of one rank (IGLOBAL, channel.h:76);
+        # pencil operators then act on arrays [i1-i0][NZ][NY].  The FFT operators need the full grid.
+        i = np.arange(self.nx) if i_range is None else np.arange(i_range[0], i_range[1])
         self.kx_int = np.where(i < self.nx // 2, i, i - self.nx)          # RK3_kernels.cu:45
         self.kz_int = np.arange(self.nz)
         # wavenumbers in the state type (RK3_kernels.cu:45-54) ...
