@@ -63,6 +63,7 @@ def load_library():
         "chan_calc_uw": [vp, vp, vp, vp, vp], "chan_convolution": [vp, vp, vp, vp, vp, vp, vp],
         "chan_calc_hvg": [vp, vp, vp, vp], "chan_impose_symmetry": [vp, vp, vp],
         "chan_fft_backward_transpose": [vp, vp, vp],
+        "chan_deriv_y_pencils_static": [vp, vp, C.c_long],
         "chan_partition": [ci, ci, ci, C.POINTER(ci), C.POINTER(ci)],
         "chan_active_kx": [ci], "chan_active_kz": [ci],
     }
@@ -273,6 +274,12 @@ class Channel:
         a, b = self._dev(u), self._dev(v)
         self._ck(self.L.chan_impose_symmetry(self.h, a.data_ptr(), b.data_ptr()), "chan_impose_symmetry")
         return a.cpu().numpy(), b.cpu().numpy()
+
+    def deriv_y_pencils_static(self, dev_tensor, n_pencils):
+        """chan_deriv_y_pencils_static on a torch CUDA tensor holding [n_pencils][NY] complex, in place.
+        Allocation-free inside the library (its scratch is a fixed array in the library image)."""
+        self._ck(self.L.chan_deriv_y_pencils_static(self.h, dev_tensor.data_ptr(), int(n_pencils)), "chan_deriv_y_pencils_static")
+        return dev_tensor
 
     def fftBackwardTranspose(self, u):
         """-> real [NY][NX][2NZ-2] (pad columns dropped)."""

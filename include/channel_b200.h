@@ -134,6 +134,20 @@ int chan_impose_symmetry(chan_handle* h, void* u_dev, void* v_dev);             
  * [NY][NX][2NZ] (2NZ-2 points + 2 pad floats per row, fft.c:17-21), out of place */
 int chan_fft_backward_transpose(chan_handle* h, const void* u_dev, void* phys_dev);
 
+/* ---- allocation-free variant ------------------------------------------------------
+ * No counterpart in the reference.  Compact d/dy (the arithmetic of chan_deriv_y) of
+ * n_pencils consecutive y-pencils, complex [n_pencils][NY] with y fastest — any run of
+ * (i,k) pencils of a reference-layout array — in place, on the handle's stream, for
+ * hosts that cannot allocate device memory when they call (all of it already belongs
+ * to their own arena, or they may not take cudaMalloc's device-wide synchronisation).
+ * The forward-sweep scratch is a fixed 16 MiB array inside the library image, held by
+ * every GPU that loads the library until exit: NY*2*n_pencils must not exceed
+ * 2097152 doubles, otherwise CHAN_ERR_ARG is returned and nothing runs.  The call makes
+ * no cudaMalloc/cudaFree and no allocating library call.  The first call on a device
+ * resolves the array's address: issue it before any stream capture.  All calls share
+ * the array, so calls that may overlap on the GPU must be serialised by the caller. */
+int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_pencils);
+
 /* ---- slab decomposition (main.c:47, channel.h:71-79), pure host arithmetic --- */
 /* splits n items over `size` ranks as evenly as possible: [*start, *start+*count) */
 int chan_partition(int n, int size, int rank, int* start, int* count);
