@@ -26,7 +26,7 @@ def build_lib(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    headers = [os.path.join(CSRC, "chan_internal.h"), os.path.join(HERE, "..", "include", "channel_b200.h")]
+    headers = [os.path.join(CSRC, h) for h in ("chan_internal.h", "fft_core.cuh", "plane_core.cuh", "fft_twiddle_consts.h")] + [os.path.join(HERE, "..", "include", "channel_b200.h")]
     jobs = []
     objs = []
     for s in SOURCES:

@@ -53,6 +53,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (cfg->nx < 8 || cfg->ny < 8 || cfg->nz < 5 || (cfg->nx & 1)) return set_err(h, CHAN_ERR_ARG, "grid %dx%dx%d: need even NX>=8, NY>=8, NZ>=5", cfg->nx, cfg->ny, cfg->nz);
   if (cfg->size != 1 || cfg->rank != 0) return set_err(h, CHAN_ERR_ARG, "this build runs one slab per handle; multi-GPU runs go through the python launcher");
   h->prec = cfg->precision;
+  {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
+    struct { const char* name; int* v; int def; } knobs[] = {
+      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 256 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 } };
+    for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
+  }
   Dims& d = h->d;
   d.nx = cfg->nx; d.ny = cfg->ny; d.nz = cfg->nz; d.nzp = 2 * cfg->nz - 2;
   d.kxmax = d.nx / 3; d.Kx = 2 * d.kxmax + 1; d.Kz = d.nzp / 3 + 1;          // dealias.cu:37 (integer divisions)
@@ -70,9 +76,11 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if ((rc = alloc_dev(h, (void**)&h->sB, chain))) return rc;
   if ((rc = alloc_dev(h, (void**)&h->sC, chain))) return rc;
   if ((rc = alloc_dev(h, (void**)&h->sP, chain / 2))) return rc;
-  // plane batch: keep the x-transformed staging of one batch (6 fields) inside the L2
+  // plane batch: the plane kernels are latency/issue-bound, not bandwidth-bound (profiles/r01_*): larger
+  // launches win over L2 residency of the staging, so take as many planes per launch group as fit in
+  // 1.5 GiB of staging (all of them up to Re_tau=550; 10 at Re_tau=1000 in fp64)
   const size_t plane_q = (size_t)6 * d.nx * d.Kz * csize(h);
-  int pb = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(48u << 20) / plane_q);
+  int pb = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(1536u << 20) / plane_q);
   if (pb < 1) pb = 1;
   if (pb > d.nyl) pb = d.nyl;
   h->plane_batch = pb;
@@ -94,7 +102,7 @@ extern "C" void chan_destroy(chan_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
-                   h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
+                   h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }

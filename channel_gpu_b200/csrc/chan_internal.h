@@ -48,6 +48,8 @@ struct FftPlan {
   int radix[16];
   int span[16];                 // sub-transform size entering stage t (1, r0, r0*r1, ...)
   const void* tw;               // T2[n]: exp(-2 pi i k / n)
+  const int* inv;               // digit-reversed position -> natural index
+  const int* pos;               // natural index -> digit-reversed position
 };
 
 // ---- handle ---------------------------------------------------------------
@@ -89,12 +91,13 @@ struct chan_handle {
   // tables
   double* ytab_store; chan::YTabs yt;
   void *tw_x, *tw_z; chan::FftPlan px, pz;
-  int *invx, *invz;             // digit-reversed position -> natural index (export path only)
+  int *invx, *invz, *posx, *posz;   // digit-reversal tables of the two plans
   void *mean_a, *mean_b;        // host-mesh differences in T (meanUevol.c:230-231)
   void *mean_u, *mean_N, *mean_uw, *mean_tmp;   // T[NY] (+ scratch)
   chan::Scalars* sc;            // device
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
@@ -110,6 +113,8 @@ int set_err(chan_handle* h, int code, const char* fmt, ...);
 
 // kernels_tables.cu
 int build_tables(chan_handle* h);
+void make_plan(FftPlan* p, int n, bool small_last, int max_radix = 16);
+int perm_pos_of(const FftPlan& p, int n);
 // kernels_pencil.cu
 int launch_pencil_pre(chan_handle* h);
 int launch_pencil_post(chan_handle* h, int n);

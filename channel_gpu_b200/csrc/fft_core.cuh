@@ -1,0 +1,158 @@
+// Hand-written mixed-radix FFT building blocks for the plane stage (kernels_plane.cu).
+// Everything here is __host__ __device__ so that tests/host/fft_host_test.cu can run the very
+// same code on the CPU, emulating the threads of a block one after the other (within a phase
+// the threads touch disjoint shared-memory elements).
+//
+// Radices 2, 3, 4 are written out; 6, 8, 12, 16 are composites done entirely in registers with
+// compile-time twiddles (fft_twiddle_consts.h, generated with
+//   python -c "import math; ..."   see channel_gpu_b200/csrc/gen note in DESIGN.md section 4).
+//
+// Index conventions.  A plan is a radix list r_0..r_{s-1} with spans m_0 = 1, m_{t+1} = m_t r_t.
+// Stage t works on groups g of m_t*r_t consecutive positions: elements g*m_t*r_t + q*m_t + k.
+//   DIT stage:  a_q *= W_{m r}^{q k};  y = DFT_r(a);  store y_p at ... + p*m + k
+//   DIF stage:  b = DFT_r(a);  b_q *= W_{m r}^{q k};  store          (the transposed graph)
+// DIT stages 0..s-1 turn digit-reversed input into natural output; DIF stages s-1..0 do the
+// opposite.  `inv[pos]` is the natural index held at digit-reversed position `pos`.
+#pragma once
+#include "fft_twiddle_consts.h"
+
+namespace chan {
+namespace fft {
+
+template <class T2> struct RealOf { typedef decltype(T2().x) type; };
+template <class T2> FFT_HD T2 mk2(typename RealOf<T2>::type a, typename RealOf<T2>::type b) { T2 r; r.x = a; r.y = b; return r; }
+template <class T2> FFT_HD T2 cadd(T2 a, T2 b) { return mk2<T2>(a.x + b.x, a.y + b.y); }
+template <class T2> FFT_HD T2 csub(T2 a, T2 b) { return mk2<T2>(a.x - b.x, a.y - b.y); }
+template <class T2> FFT_HD T2 cmul(T2 a, T2 b) { return mk2<T2>(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+// a * w for the forward transform (SIGN < 0), a * conj(w) for the inverse (SIGN > 0); w = exp(-i theta)
+template <int SIGN, class T2> FFT_HD T2 twmul(T2 a, T2 w) {
+  return SIGN < 0 ? mk2<T2>(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x) : mk2<T2>(a.x * w.x + a.y * w.y, a.y * w.x - a.x * w.y);
+}
+template <int SIGN, class T2> FFT_HD T2 muli(T2 a) { return SIGN > 0 ? mk2<T2>(-a.y, a.x) : mk2<T2>(a.y, -a.x); }   // SIGN * i * a
+
+// multiply by the compile-time twiddle W_R^j (forward) or its conjugate (inverse)
+template <int R, int SIGN, class T2> FFT_HD T2 tw_const(T2 a, int j) {
+  typedef typename RealOf<T2>::type T;
+  j = j % R;
+  if (j == 0) return a;
+  if ((4 * j) % R == 0) {                       // quarter turns: W = (-i)^(4j/R) forward
+    int qt = (4 * j) / R;
+    if (qt == 2) return mk2<T2>(-a.x, -a.y);
+    T2 t = muli<SIGN, T2>(a);                    // SIGN*i*a ; forward W^(R/4) = -i = SIGN*i for SIGN=-1
+    return qt == 1 ? t : mk2<T2>(-t.x, -t.y);
+  }
+  T2 w = mk2<T2>((T)fft_tw_cos(R, j), (T)(-fft_tw_sin(R, j)));
+  return twmul<SIGN, T2>(a, w);
+}
+
+// ---- in-register DFTs, natural order in and out:  y_p = sum_q a_q exp(SIGN 2 pi i p q / R) -------
+template <int R, int SIGN, class T2> struct Dft;
+template <int SIGN, class T2> struct Dft<1, SIGN, T2> { FFT_HD static void run(T2*) {} };
+template <int SIGN, class T2> struct Dft<2, SIGN, T2> {
+  FFT_HD static void run(T2* a) { T2 t = a[0]; a[0] = cadd(t, a[1]); a[1] = csub(t, a[1]); }
+};
+template <int SIGN, class T2> struct Dft<3, SIGN, T2> {
+  FFT_HD static void run(T2* a) {
+    typedef typename RealOf<T2>::type T;
+    const T h = (T)0.86602540378443864676372317075294;
+    T2 t1 = cadd(a[1], a[2]);
+    T2 t2 = mk2<T2>(a[0].x - (T)0.5 * t1.x, a[0].y - (T)0.5 * t1.y);
+    T2 d = csub(a[1], a[2]);
+    T2 t3 = muli<SIGN, T2>(mk2<T2>(h * d.x, h * d.y));
+    a[0] = cadd(a[0], t1); a[1] = cadd(t2, t3); a[2] = csub(t2, t3);
+  }
+};
+template <int SIGN, class T2> struct Dft<4, SIGN, T2> {
+  FFT_HD static void run(T2* a) {
+    T2 t0 = cadd(a[0], a[2]), t1 = csub(a[0], a[2]), t2 = cadd(a[1], a[3]), t3 = muli<SIGN, T2>(csub(a[1], a[3]));
+    a[0] = cadd(t0, t2); a[2] = csub(t0, t2); a[1] = cadd(t1, t3); a[3] = csub(t1, t3);
+  }
+};
+// R = R1*R2: n = R1*n2 + n1, k = k2 + R2*k1
+template <int R1, int R2, int SIGN, class T2> FFT_HD void dft_composite(T2* a) {
+  constexpr int R = R1 * R2;
+  T2 s[R1][R2];
+#pragma unroll
+  for (int n1 = 0; n1 < R1; n1++) {
+#pragma unroll
+    for (int n2 = 0; n2 < R2; n2++) s[n1][n2] = a[R1 * n2 + n1];
+    Dft<R2, SIGN, T2>::run(s[n1]);
+#pragma unroll
+    for (int k2 = 1; k2 < R2; k2++) s[n1][k2] = tw_const<R, SIGN, T2>(s[n1][k2], n1 * k2);
+  }
+#pragma unroll
+  for (int k2 = 0; k2 < R2; k2++) {
+    T2 c[R1];
+#pragma unroll
+    for (int n1 = 0; n1 < R1; n1++) c[n1] = s[n1][k2];
+    Dft<R1, SIGN, T2>::run(c);
+#pragma unroll
+    for (int k1 = 0; k1 < R1; k1++) a[k2 + R2 * k1] = c[k1];
+  }
+}
+template <int SIGN, class T2> struct Dft<6, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 3, SIGN, T2>(a); } };
+template <int SIGN, class T2> struct Dft<8, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 4, SIGN, T2>(a); } };
+template <int SIGN, class T2> struct Dft<12, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<3, 4, SIGN, T2>(a); } };
+template <int SIGN, class T2> struct Dft<16, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<4, 4, SIGN, T2>(a); } };
+
+// ---- stage twiddles W_{mR}^{q k}, q = 1..R-1 -----------------------------------------------------
+// fp64: one table load, the other powers by squaring/multiplying (log depth): the stages are bound
+// by the shared-memory / L1 pipe, fp64 FMAs are spare.  fp32: direct table loads (accuracy).
+template <class T2> struct UsePowers { static const bool value = sizeof(typename RealOf<T2>::type) == 8; };
+
+#ifdef __CUDA_ARCH__
+#define FFT_LDG(p) __ldg(p)
+#else
+#define FFT_LDG(p) (*(p))
+#endif
+
+template <int R, int SIGN, class T2> FFT_HD void apply_twiddles(T2* a, const T2* tw, int k, int tws) {
+  if (R == 1) return;
+  if (UsePowers<T2>::value) {
+    T2 pw[R > 1 ? R : 2];
+    pw[1] = FFT_LDG(tw + k * tws);
+#pragma unroll
+    for (int q = 2; q < R; q++) pw[q] = (q & 1) ? cmul(pw[q - 1], pw[1]) : cmul(pw[q / 2], pw[q / 2]);
+#pragma unroll
+    for (int q = 1; q < R; q++) a[q] = twmul<SIGN, T2>(a[q], pw[q]);
+  } else {
+#pragma unroll
+    for (int q = 1; q < R; q++) a[q] = twmul<SIGN, T2>(a[q], FFT_LDG(tw + q * k * tws));
+  }
+}
+
+// ---- a whole shared-memory stage ----------------------------------------------------------------
+// element (pos, line) lives at s[pos*st + line_index(l)], line_index(l) = (l / nact) * nper + l % nact
+// (nact of every nper interleaved lines take part; nlines = number of participating lines)
+template <class T2, int R, int SIGN, bool DIT>
+FFT_HD void smem_stage(T2* s, int n, int m, int st, int nlines, int nact, int nper, const T2* tw, int tid, int nthr) {
+  const int nb = n / R, tws = n / (m * R);
+  for (int b = tid; b < nb * nlines; b += nthr) {
+    int l = b % nlines, bf = b / nlines;
+    int li = (l / nact) * nper + l % nact;
+    int g = bf / m, k = bf - g * m;
+    T2* p = s + (size_t)(g * m * R + k) * st + li;
+    T2 a[R];
+#pragma unroll
+    for (int q = 0; q < R; q++) a[q] = p[(size_t)q * m * st];
+    if (DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
+    Dft<R, SIGN, T2>::run(a);
+    if (!DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
+#pragma unroll
+    for (int q = 0; q < R; q++) p[(size_t)q * m * st] = a[q];
+  }
+}
+
+#define FFT_DISPATCH_RADIX(r, CALL)                                                    \
+  switch (r) {                                                                         \
+    case 2: { constexpr int RR = 2; CALL; } break;                                     \
+    case 3: { constexpr int RR = 3; CALL; } break;                                     \
+    case 4: { constexpr int RR = 4; CALL; } break;                                     \
+    case 6: { constexpr int RR = 6; CALL; } break;                                     \
+    case 8: { constexpr int RR = 8; CALL; } break;                                     \
+    case 12: { constexpr int RR = 12; CALL; } break;                                   \
+    default: { constexpr int RR = 16; CALL; } break;                                   \
+  }
+
+}  // namespace fft
+}  // namespace chan

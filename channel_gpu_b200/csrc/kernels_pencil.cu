@@ -83,6 +83,20 @@ __device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) 
 
 __device__ __forceinline__ int phys_row(int dir, int jj, int ny) { return dir ? ny - 1 - jj : jj; }
 
+// The sweeps are latency-bound (one dependent row per thread in flight): pull the rows a few steps
+// ahead into L2, one request per 128-byte line (lanes 0 and 16 of the warp's 256-byte row segment).
+#define CHAN_PF_ROWS 6
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+struct Prefetch {
+  bool lead; int ny;
+  __device__ __forceinline__ Prefetch(int ny_) : lead((threadIdx.x & 15) == 0), ny(ny_) {}
+  // row j + d*CHAN_PF_ROWS of an array with `stride` elements per row; p points at this thread's element of row j
+  template <typename E> __device__ __forceinline__ void operator()(const E* p, long stride, int j, int d) const {
+    int jn = j + d * CHAN_PF_ROWS;
+    if (lead && jn >= 0 && jn < ny) pf_l2(p + (long)d * CHAN_PF_ROWS * stride);
+  }
+};
+
 template <typename T2, typename T>
 __device__ __forceinline__ T own(const T2& z, int c) { return c ? z.y : z.x; }
 template <typename T2, typename T>
@@ -237,9 +251,11 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   double det = q.dv1 * p.dv2 - p.dv1 * q.dv2;
   double c1 = p.dv2 * dvm - q.dv2 * dvp; c1 = -c1 / det;
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
+  const Prefetch pf(ny);
   for (int j = 0; j < ny; j++) {
-    BcFun f = bc_functions(l1, l2, D, __ldg(a.yt.y + j));
     long i = (long)j * st + md.e;
+    pf(phi + i, st, j, 1); pf(v + i, st, j, 1); pf(dv + i, st, j, 1);
+    BcFun f = bc_functions(l1, l2, D, __ldg(a.yt.y + j));
     double pp = (double)phi[i], vv = (double)v[i], dd = (double)dv[i];
     pp = pp + c1 * f.ddv1 + c2 * f.ddv2;
     dd = dd + c1 * f.dv1 + c2 * f.dv2;
@@ -272,11 +288,13 @@ __global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
   if (!setup(a, md, wv)) return;
   const long st = 2 * a.M; const int ny = a.ny; const int c = md.c;
   const bool with_mean = md.zero_mode && a.use_mean;
+  const Prefetch pf(ny);
   // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w
   {
     ElimD1 eu, ew;
     for (int j = 0; j < ny; j++) {
       long cm = (long)j * a.M + md.m;
+      if (a.op != OP_OMEGA) { pf(a.dv + cm, a.M, j, 1); pf(a.g + cm, a.M, j, 1); }
       T u, w;
       if (a.op == OP_OMEGA) { u = ((const T*)a.u)[(long)j * st + md.e]; w = ((const T*)a.w)[(long)j * st + md.e]; }
       else {
@@ -292,6 +310,8 @@ __global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
     double xu = 0.0, xw = 0.0;
     for (int j = ny - 1; j >= 0; j--) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
+      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.v + cm, a.M, j, -1);
+      if (a.op != OP_OMEGA) { pf(a.dv + cm, a.M, j, -1); pf(a.g + cm, a.M, j, -1); }
       double cp = __ldg(a.yt.d1[0].cp + j);
       xu = a.sA[re] - cp * xu; xw = a.sB[re] - cp * xw;
       T dudy = (T)xu, dwdy = (T)xw;
@@ -333,11 +353,13 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
   const T s = wv.sc;
   const T* phiR = (const T*)a.phi; const T* gR = (const T*)a.g;
   const T2* H1 = a.ox; const T2* H3 = a.oz; const T* H2R = (const T*)a.oy;
+  const Prefetch pf(ny);
   // P1 (up): eliminate d/dy of phi, g and hv = -i (k1 H1 + k3 H3)  (calcHvgkernel, nonLinear_kernels.cu:129-130)
   {
     ElimD1 ep, eg, eh;
     for (int j = 0; j < ny; j++) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + e;
+      pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
       T h1p = other<T2, T>(H1[cm], c), h3p = other<T2, T>(H3[cm], c);
       T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
       ep.step(a.yt.d1[0], 0, j, ny, (double)phiR[re], a.sA, st, e);
@@ -351,6 +373,7 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     double xp = 0.0, xg = 0.0, xh = 0.0;
     for (int jj = 0; jj < ny; jj++) {
       int j = ny - 1 - jj; long re = (long)j * st + e;
+      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sC + re, st, j, -1);
       double cp = __ldg(a.yt.d1[0].cp + j);
       xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg; xh = a.sC[re] - cp * xh;
       a.sC[re] = rnd<T>(xh);
@@ -367,6 +390,10 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     double xp = 0.0, xg = 0.0;
     for (int j = 0; j < ny; j++) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + e;
+      pf(a.sA + re, st, j, 1); pf(a.sB + re, st, j, 1); pf(a.sC + re, st, j, 1);
+      pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(H2R + re, st, j, 1);
+      pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
+      pf((const T*)a.Rphi + re, st, j, 1); pf((const T*)a.Rg + re, st, j, 1);
       double cp = __ldg(a.yt.d1[1].cp + (ny - 1 - j));
       xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
       T pyy = (T)xp, gyy = (T)xg;
@@ -392,6 +419,7 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     double xp = 0.0, xg = 0.0;
     for (int jj = 0; jj < ny; jj++) {
       int j = ny - 1 - jj; long re = (long)j * st + e;
+      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sP + (long)j * a.M + md.m, a.M, j, -1);
       double cp = a.sP[(long)j * a.M + md.m];
       xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
       // both components of a mode share the pivot row: every lane must have read row j before
@@ -409,6 +437,7 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     double xv = 0.0;
     for (int j = 0; j < ny; j++) {
       long re = (long)j * st + e;
+      pf(a.sA + re, st, j, 1); pf(a.sP + (long)j * a.M + md.m, a.M, j, 1);
       xv = a.sA[re] - a.sP[(long)j * a.M + md.m] * xv;
       ((T*)a.v)[re] = (T)xv;
       ev.step(a.yt.d1[0], 0, j, ny, rnd<T>(xv), a.sA, st, e);
@@ -420,6 +449,7 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     double x = 0.0;
     for (int j = ny - 1; j >= 0; j--) {
       long re = (long)j * st + e;
+      pf(a.sA + re, st, j, -1);
       x = a.sA[re] - __ldg(a.yt.d1[0].cp + j) * x;
       ((T*)a.dv)[re] = (T)x;
       if (j == ny - 1) dvp = rnd<T>(x);

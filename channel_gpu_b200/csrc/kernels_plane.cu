@@ -5,98 +5,27 @@
 // product u x omega (rotorkernel, convolution_kernels.cu:69-148), the velocity
 // maxima of calcUmax (fft.c:143-169) and imposeSymetry (imposeSymetry.c:5-18).
 //
-// All transforms are hand-written shared-memory mixed-radix (4,2,3) FFTs.  cuFFT
-// is not linked.  Design points:
-//  * PERMUTATION-FREE.  Inverse transforms run decimation-in-frequency (natural
-//    order in, digit-reversed order out), forward transforms decimation-in-time
-//    with the same radix schedule (digit-reversed in, natural out).  Physical
-//    space is only ever used pointwise (products, maxima), so x and z stay
-//    digit-reversed there and no reorder pass or index table exists on the hot
-//    path.
-//  * BATCH-FASTEST shared-memory layout s[pos][line]: the lanes of a warp work
-//    on the same butterfly of neighbouring lines, so every stage, whatever its
-//    stride, is bank-conflict free.
-//  * TWO-FOR-ONE real transforms in z: the same field at two neighbouring x is
-//    packed as one complex line (a + i b), halving the z-FFT work; Hermitian
-//    unpacking happens in the store.
-//  * The physical fields never touch HBM: C2R x6 -> u x omega -> R2C x3 happen
-//    inside one kernel per (plane, x-pair).  The x-transformed intermediates
-//    Q[f][plane][x][kz] are produced and consumed per PLANE BATCH sized to stay
+// All transforms are hand-written shared-memory mixed-radix FFTs (radices up to
+// 16 in registers, fft_core.cuh); cuFFT is not linked.  Design points (details
+// in plane_core.cuh):
+//  * first / last stages fused with the global loads and stores; in z the last
+//    inverse stage, u x omega and the first forward stage are one register pass,
+//    so a 384-point line makes 3 shared-memory round trips instead of 10;
+//  * inverse = decimation in time, forward = decimation in frequency with the
+//    same radix schedule: physical space is in natural order and no reorder pass
+//    exists;
+//  * batch-fastest shared-memory layout s[pos][line]: conflict-free at every
+//    stride;
+//  * two-for-one real transforms in z: the same field at two neighbouring x is
+//    one complex line (a + i b);
+//  * the physical fields never touch HBM; the x-transformed staging
+//    Q[f][plane][x][kz] is produced and consumed per plane batch sized to stay
 //    resident in the 126 MB L2.
-#include "chan_internal.h"
+#include "plane_core.cuh"
 
 namespace chan {
+using namespace fft;
 
-template <typename T2> __device__ __forceinline__ T2 mk(decltype(T2().x) a, decltype(T2().x) b) { T2 r; r.x = a; r.y = b; return r; }
-template <typename T2> __device__ __forceinline__ T2 cadd(T2 a, T2 b) { return mk<T2>(a.x + b.x, a.y + b.y); }
-template <typename T2> __device__ __forceinline__ T2 csub(T2 a, T2 b) { return mk<T2>(a.x - b.x, a.y - b.y); }
-// a * w (SIGN<0) or a * conj(w) (SIGN>0)
-template <typename T2, int SIGN> __device__ __forceinline__ T2 ctw(T2 a, T2 w) {
-  if (SIGN < 0) return mk<T2>(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x);
-  return mk<T2>(a.x * w.x + a.y * w.y, a.y * w.x - a.x * w.y);
-}
-// multiply by SIGN * i
-template <typename T2, int SIGN> __device__ __forceinline__ T2 muli(T2 a) {
-  return SIGN > 0 ? mk<T2>(-a.y, a.x) : mk<T2>(a.y, -a.x);
-}
-
-template <typename T2, int SIGN> __device__ __forceinline__ void bf2(T2* a) {
-  T2 t = a[0]; a[0] = cadd(t, a[1]); a[1] = csub(t, a[1]);
-}
-template <typename T2, int SIGN> __device__ __forceinline__ void bf4(T2* a) {
-  T2 t0 = cadd(a[0], a[2]), t1 = csub(a[0], a[2]), t2 = cadd(a[1], a[3]), t3 = muli<T2, SIGN>(csub(a[1], a[3]));
-  a[0] = cadd(t0, t2); a[2] = csub(t0, t2); a[1] = cadd(t1, t3); a[3] = csub(t1, t3);
-}
-template <typename T2, int SIGN> __device__ __forceinline__ void bf3(T2* a) {
-  typedef decltype(T2().x) T;
-  const T h = (T)0.86602540378443864676372317075294;
-  T2 t1 = cadd(a[1], a[2]);
-  T2 t2 = mk<T2>(a[0].x - (T)0.5 * t1.x, a[0].y - (T)0.5 * t1.y);
-  T2 d = csub(a[1], a[2]);
-  T2 t3 = muli<T2, SIGN>(mk<T2>(h * d.x, h * d.y));
-  a[0] = cadd(a[0], t1); a[1] = cadd(t2, t3); a[2] = csub(t2, t3);
-}
-
-// One radix-R stage over LINES interleaved lines (element (pos, line) at s[pos*STRIDE + line]).
-template <typename T2, int R, int LINES, int STRIDE, bool DIF, int SIGN>
-__device__ __forceinline__ void fft_stage(T2* s, int n, int m, const T2* __restrict__ tw, int tid, int nthr) {
-  const int nb = n / R;
-  const int tws = n / (m * R);
-  for (int b = tid; b < nb * LINES; b += nthr) {
-    int line = b % LINES, bf = b / LINES;
-    int g = bf / m, k = bf - g * m;
-    T2* p = s + (size_t)(g * m * R + k) * STRIDE + line;
-    T2 a[R];
-#pragma unroll
-    for (int q = 0; q < R; q++) a[q] = p[(size_t)q * m * STRIDE];
-    if (!DIF) {
-#pragma unroll
-      for (int q = 1; q < R; q++) a[q] = ctw<T2, SIGN>(a[q], __ldg(tw + q * k * tws));
-    }
-    if (R == 2) bf2<T2, SIGN>(a); else if (R == 3) bf3<T2, SIGN>(a); else bf4<T2, SIGN>(a);
-    if (DIF) {
-#pragma unroll
-      for (int q = 1; q < R; q++) a[q] = ctw<T2, SIGN>(a[q], __ldg(tw + q * k * tws));
-    }
-#pragma unroll
-    for (int q = 0; q < R; q++) p[(size_t)q * m * STRIDE] = a[q];
-  }
-  __syncthreads();
-}
-
-template <typename T2, int LINES, int STRIDE, bool DIF, int SIGN>
-__device__ __forceinline__ void fft_smem(T2* s, const FftPlan& pl, int tid, int nthr) {
-  const T2* tw = (const T2*)pl.tw;
-  for (int i = 0; i < pl.nstage; i++) {
-    int t = DIF ? pl.nstage - 1 - i : i;
-    int r = pl.radix[t], m = pl.span[t];
-    if (r == 4) fft_stage<T2, 4, LINES, STRIDE, DIF, SIGN>(s, pl.n, m, tw, tid, nthr);
-    else if (r == 2) fft_stage<T2, 2, LINES, STRIDE, DIF, SIGN>(s, pl.n, m, tw, tid, nthr);
-    else fft_stage<T2, 3, LINES, STRIDE, DIF, SIGN>(s, pl.n, m, tw, tid, nthr);
-  }
-}
-
-// -------------------------------------------------------------------------------
 template <typename T>
 struct XArgs {
   typedef typename Vec2<T>::type T2;
@@ -104,75 +33,56 @@ struct XArgs {
   T2* Q;                          // [f][pb][NX][Kz]
   FftPlan px;
   int nx, Kx, Kz, kxmax, j_start, pb; long M;
+  int dbg_skip;                   // timing ablation only (CHAN_TUNE_X_SKIP bit 0: inverse, bit 1: forward returns at once)
   T scale;                        // forward only: divide by this when != 0 (normalizekernel, dealias.cu:72-97)
 };
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
-// x inverse: compact spectral rows -> zero-padded NX line -> DIF inverse -> Q (x digit-reversed)
+// x inverse: compact spectral rows -> (zero pad) -> natural-order physical x line, still spectral in z
 template <typename T, int TK>
-__global__ void __launch_bounds__(256) xfft_inv_kernel(XArgs<T> a) {
+__global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   T2* s = (T2*)smem_raw;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int kz0 = blockIdx.x * TK, jb = blockIdx.y, f = blockIdx.z;
-  const int j = a.j_start + jb;
-  const T2* src = a.src[f] + (size_t)j * a.M;
-  for (int idx = tid; idx < a.nx * TK; idx += nthr) {
-    int pos = idx / TK, t = idx - pos * TK, kz = kz0 + t;
-    int ikx = pos <= a.kxmax ? pos : (pos >= a.nx - a.kxmax ? pos - a.nx + a.Kx : -1);
-    T2 v = mk<T2>(0, 0);
-    if (ikx >= 0 && kz < a.Kz) v = src[(size_t)ikx * a.Kz + kz];
-    s[idx] = v;
-  }
-  __syncthreads();
-  fft_smem<T2, TK, TK, true, +1>(s, a.px, tid, nthr);
+  if (a.dbg_skip & 1) return;
+  const PlanT<T2> pl = plan_of<T2>(a.px);
+  const T2* src = a.src[f] + (size_t)(a.j_start + jb) * a.M;
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  for (int idx = tid; idx < a.nx * TK; idx += nthr) {
-    int pos = idx / TK, t = idx - pos * TK, kz = kz0 + t;
-    if (kz < a.Kz) q[(size_t)pos * a.Kz + kz] = s[idx];
-  }
+  FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s, src, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
+  __syncthreads();
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
 }
 
-// x forward: Q (x digit-reversed) -> DIT forward -> truncated compact spectral rows
+// x forward: natural-order x line -> truncated compact spectral rows
 template <typename T, int TK>
-__global__ void __launch_bounds__(256) xfft_fwd_kernel(XArgs<T> a) {
+__global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   T2* s = (T2*)smem_raw;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int kz0 = blockIdx.x * TK, jb = blockIdx.y, f = blockIdx.z;
-  const int j = a.j_start + jb;
+  if (a.dbg_skip & 2) return;
+  const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  for (int idx = tid; idx < a.nx * TK; idx += nthr) {
-    int pos = idx / TK, t = idx - pos * TK, kz = kz0 + t;
-    s[idx] = kz < a.Kz ? q[(size_t)pos * a.Kz + kz] : mk<T2>(0, 0);
-  }
+  T2* dst = a.dst[f] + (size_t)(a.j_start + jb) * a.M;
+  FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
-  fft_smem<T2, TK, TK, false, -1>(s, a.px, tid, nthr);
-  T2* dst = a.dst[f] + (size_t)j * a.M;
-  for (int idx = tid; idx < a.Kx * TK; idx += nthr) {
-    int ikx = idx / TK, t = idx - ikx * TK, kz = kz0 + t;
-    int pos = ikx <= a.kxmax ? ikx : ikx - a.Kx + a.nx;
-    if (kz < a.Kz) {
-      T2 v = s[pos * TK + t];
-      if (a.scale != (T)0) { v.x /= a.scale; v.y /= a.scale; }
-      dst[(size_t)ikx * a.Kz + kz] = v;
-    }
-  }
+  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, dst, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
 // -------------------------------------------------------------------------------
-enum { ZMODE_ROTOR = 0, ZMODE_IDENTITY = 1, ZMODE_EXPORT = 2 };
-
 template <typename T>
 struct ZArgs {
   typedef typename Vec2<T>::type T2;
   T2* Q; FftPlan pz;
-  int nx, nzp, Kz, pb, j_start;
+  int dbg_stop;                    // >0: timing ablation only (CHAN_TUNE_Z_STOP): return after phase N
+  int nx, nzp, Kz, pb, j_start, XP, SS;   // SS: shared-memory elements per position (>= XP*NIN)
   T n2;                            // (T)N2: the reference divides by the int N2 (convolution_kernels.cu:107-121)
   unsigned long long* umax_bits;   // 3 slots
-  // export only
-  T* phys; const int* invx; const int* invz; int nz;
+  T* phys; int nz;                 // export only: real [NY][NX][2NZ]
 };
 
 __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double v) {
@@ -180,83 +90,56 @@ __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double 
 }
 
 template <typename T, int MODE>
-__global__ void __launch_bounds__(256) zstage_kernel(ZArgs<T> a) {
+__global__ void __launch_bounds__(256, 2) zstage_kernel(ZArgs<T> a) {
   typedef typename Vec2<T>::type T2;
-  constexpr int NIN = MODE == ZMODE_ROTOR ? 6 : (MODE == ZMODE_IDENTITY ? 2 : 1);
-  constexpr int NOUT = MODE == ZMODE_ROTOR ? 3 : (MODE == ZMODE_IDENTITY ? 2 : 0);
-  constexpr int ST = NIN;
+  constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
+  constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
   T2* s = (T2*)smem_raw;
   __shared__ double red[3][8];
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int xp = blockIdx.x, jb = blockIdx.y;
-  const int n = a.nzp;
+  const int xp0 = blockIdx.x * a.XP, jb = blockIdx.y;
+  if (a.dbg_stop == 9) return;
+  const int nxp_valid = min(a.XP, a.nx / 2 - xp0);
+  const int ST = a.XP * NIN;
+  const PlanT<T2> pl = plan_of<T2>(a.pz);
   const size_t fstride = (size_t)a.pb * a.nx * a.Kz;
-  T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp) * a.Kz;     // field 0, x = 2xp ; x+1 is Kz further
-  for (int idx = tid; idx < n * ST; idx += nthr) s[idx] = mk<T2>(0, 0);
+  T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
+  FFT_DISPATCH_RADIX(pl.radix[0], (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
-  // two-for-one packing: Z = A(x0) + i A(x1), Hermitian-extended; imaginary part of the kz=0 bin is
-  // dropped, as a C2R transform does
-  for (int idx = tid; idx < a.Kz * NIN; idx += nthr) {
-    int f = idx / a.Kz, k = idx - f * a.Kz;
-    T2 A = q0[f * fstride + k], B = q0[f * fstride + a.Kz + k];
-    if (k == 0) s[f] = mk<T2>(A.x, B.x);
-    else {
-      s[(size_t)k * ST + f] = mk<T2>(A.x - B.y, A.y + B.x);
-      s[(size_t)(n - k) * ST + f] = mk<T2>(A.x + B.y, B.x - A.y);
-    }
+  if (a.dbg_stop == 1) return;
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, t, a.SS, ST, ST, ST, tid, nthr); __syncthreads(); }
+  if (a.dbg_stop == 2) return;
+  T um[3] = { 0, 0, 0 };
+  T* phys = 0; size_t pxs = 0;
+  if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
+  switch (pl.radix[pl.nstage - 1]) {
+    case 2: z_mid_fused<T2, 2, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 3: z_mid_fused<T2, 3, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    default: z_mid_fused<T2, 4, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
-  __syncthreads();
-  fft_smem<T2, NIN, ST, true, +1>(s, a.pz, tid, nthr);
-  if (MODE == ZMODE_ROTOR) {
-    T mu = 0, mv = 0, mw = 0;
-    for (int i = tid; i < n; i += nthr) {
-      T2* p = s + (size_t)i * ST;
-      T2 u = p[0], v = p[1], w = p[2], ox = p[3], oy = p[4], oz = p[5];
-      mu = fmax(mu, fmax(fabs(u.x), fabs(u.y))); mv = fmax(mv, fmax(fabs(v.x), fabs(v.y))); mw = fmax(mw, fmax(fabs(w.x), fabs(w.y)));
-      u.x /= a.n2; v.x /= a.n2; w.x /= a.n2; u.y /= a.n2; v.y /= a.n2; w.y /= a.n2;
-      ox.x /= a.n2; oy.x /= a.n2; oz.x /= a.n2; ox.y /= a.n2; oy.y /= a.n2; oz.y /= a.n2;
-      p[0] = mk<T2>(v.x * oz.x - w.x * oy.x, v.y * oz.y - w.y * oy.y);
-      p[1] = mk<T2>(w.x * ox.x - u.x * oz.x, w.y * ox.y - u.y * oz.y);
-      p[2] = mk<T2>(u.x * oy.x - v.x * ox.x, u.y * oy.y - v.y * ox.y);
-    }
-    // block max -> one atomic per block and component
-    double r3[3] = { (double)mu, (double)mv, (double)mw };
+  if (MODE == ZM_EXPORT) return;
+  if (a.dbg_stop == 3) return;
+  if (MODE == ZM_ROTOR) {      // block max -> one atomic per block and component
 #pragma unroll
     for (int c = 0; c < 3; c++) {
-      double v = r3[c];
+      double v = (double)um[c];
       for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
       if ((tid & 31) == 0) red[c][tid >> 5] = v;
     }
-    __syncthreads();
-    if (tid < 3) {
-      double v = 0; for (int wi = 0; wi < (nthr >> 5); wi++) v = fmax(v, red[tid][wi]);
-      atomic_max_pos(a.umax_bits + tid, v);
-    }
-  }
-  if (MODE == ZMODE_EXPORT) {
-    const int j = a.j_start + jb;
-    const int x0 = a.invx[2 * xp], x1 = a.invx[2 * xp + 1];
-    T* o0 = a.phys + ((size_t)j * a.nx + x0) * (2 * a.nz);
-    T* o1 = a.phys + ((size_t)j * a.nx + x1) * (2 * a.nz);
-    for (int i = tid; i < n; i += nthr) { int z = a.invz[i]; T2 v = s[i]; o0[z] = v.x; o1[z] = v.y; }
-    if (tid < 2) { o0[n + tid] = 0; o1[n + tid] = 0; }
-    return;
   }
   __syncthreads();
-  fft_smem<T2, NOUT, ST, false, -1>(s, a.pz, tid, nthr);
-  // Hermitian unpacking of the pair and truncation to kz < Kz
-  for (int idx = tid; idx < a.Kz * NOUT; idx += nthr) {
-    int f = idx / a.Kz, k = idx - f * a.Kz;
-    T2 Yk = s[(size_t)k * ST + f], Yn = s[(size_t)(k ? n - k : 0) * ST + f];
-    const T h = (T)0.5;
-    q0[f * fstride + k] = mk<T2>(h * (Yk.x + Yn.x), h * (Yk.y - Yn.y));
-    q0[f * fstride + a.Kz + k] = mk<T2>(h * (Yk.y + Yn.y), h * (Yn.x - Yk.x));
+  if (MODE == ZM_ROTOR && tid < 3) {
+    double v = 0; for (int wi = 0; wi < (nthr >> 5); wi++) v = fmax(v, red[tid][wi]);
+    atomic_max_pos(a.umax_bits + tid, v);
   }
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, t, a.SS, a.XP * NOUT, NOUT, NIN, tid, nthr); __syncthreads(); }
+  if (a.dbg_stop == 4) return;
+  z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr);
 }
 
 // -------------------------------------------------------------------------------
 static int pick_tk(chan_handle* h, size_t elem) {
-  for (int tk = 8; tk >= 2; tk >>= 1)
+  for (int tk = h->tune.x_tk; tk >= 2; tk >>= 1)
     if ((size_t)h->d.nx * tk * elem <= 200 * 1024) return tk;
   return 0;
 }
@@ -268,10 +151,10 @@ static int launch_x(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
   dim3 grid((h->d.Kz + TK - 1) / TK, pb, nf);
   if (inverse) {
     CHAN_CUDA(h, cudaFuncSetAttribute(xfft_inv_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_inv_kernel<T, TK><<<grid, 256, sm, h->stream>>>(a);
+    xfft_inv_kernel<T, TK><<<grid, h->tune.x_threads, sm, h->stream>>>(a);
   } else {
     CHAN_CUDA(h, cudaFuncSetAttribute(xfft_fwd_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_fwd_kernel<T, TK><<<grid, 256, sm, h->stream>>>(a);
+    xfft_fwd_kernel<T, TK><<<grid, h->tune.x_threads, sm, h->stream>>>(a);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
@@ -290,11 +173,22 @@ static int launch_x_any(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int p
 template <typename T, int MODE>
 static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   typedef typename Vec2<T>::type T2;
-  size_t sm = (size_t)h->d.nzp * nin * sizeof(T2);
-  if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", h->d.nzp);
+  // x-pairs per block: enough positions for the register-fused middle stage to occupy the block,
+  // bounded by ~96 KB of shared memory so that two blocks fit on an SM
+  const int n = h->d.nzp, m = n / h->pz.radix[h->pz.nstage - 1];
+  const int threads = h->tune.z_threads;
+  int xp = h->tune.z_xp > 0 ? h->tune.z_xp : (3 * threads / 4 + m - 1) / m;
+  while (xp > 1 && (size_t)n * (xp * nin + 1) * sizeof(T2) > 96 * 1024) xp--;
+  if (xp > h->d.nx / 2) xp = h->d.nx / 2;
+  // an odd number of elements per position keeps the register-fused middle stage (threads stride
+  // over positions) free of bank conflicts
+  int ss = xp * nin; if (h->tune.z_pad && !(ss & 1)) ss++;
+  size_t sm = (size_t)n * ss * sizeof(T2);
+  if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
+  a.XP = xp; a.SS = ss;
   CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  dim3 grid(h->d.nx / 2, pb);
-  zstage_kernel<T, MODE><<<grid, 256, sm, h->stream>>>(a);
+  dim3 grid((h->d.nx / 2 + xp - 1) / xp, pb);
+  zstage_kernel<T, MODE><<<grid, threads, sm, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
@@ -304,7 +198,7 @@ template <typename T>
 static void fill_x(chan_handle* h, XArgs<T>& a) {
   typedef typename Vec2<T>::type T2;
   a.Q = (T2*)h->Q; a.px = h->px; a.nx = h->d.nx; a.Kx = h->d.Kx; a.Kz = h->d.Kz; a.kxmax = h->d.kxmax;
-  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0;
+  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0; a.dbg_skip = h->tune.x_skip;
 }
 template <typename T>
 static void fill_z(chan_handle* h, ZArgs<T>& a) {
@@ -312,7 +206,7 @@ static void fill_z(chan_handle* h, ZArgs<T>& a) {
   a.Q = (T2*)h->Q; a.pz = h->pz; a.nx = h->d.nx; a.nzp = h->d.nzp; a.Kz = h->d.Kz; a.nz = h->d.nz;
   a.n2 = (T)(h->d.nx * h->d.nzp);
   a.umax_bits = h->sc->umax_bits;
-  a.phys = 0; a.invx = (const int*)h->invx; a.invz = (const int*)h->invz;
+  a.phys = 0; a.XP = 1; a.SS = 0; a.dbg_stop = h->tune.z_stop;
 }
 
 template <typename T>
@@ -327,7 +221,7 @@ static int nonlinear_t(chan_handle* h) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = xf.j_start = z.j_start = h->d.j0 + js; xi.pb = xf.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 6, pb); if (rc) return rc;
-    rc = launch_z<T, ZMODE_ROTOR>(h, z, 6, pb); if (rc) return rc;
+    rc = launch_z<T, ZM_ROTOR>(h, z, 6, pb); if (rc) return rc;
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
   }
   return CHAN_OK;
@@ -345,7 +239,7 @@ static int symmetrize_t(chan_handle* h, void* fa, void* fb) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = xf.j_start = z.j_start = h->d.j0 + js; xi.pb = xf.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 2, pb); if (rc) return rc;
-    rc = launch_z<T, ZMODE_IDENTITY>(h, z, 2, pb); if (rc) return rc;
+    rc = launch_z<T, ZM_IDENTITY>(h, z, 2, pb); if (rc) return rc;
     rc = launch_x_any<T>(h, false, xf, 2, pb); if (rc) return rc;
   }
   return CHAN_OK;
@@ -362,7 +256,7 @@ static int export_t(chan_handle* h, const void* f, void* phys) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = z.j_start = h->d.j0 + js; xi.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 1, pb); if (rc) return rc;
-    rc = launch_z<T, ZMODE_EXPORT>(h, z, 1, pb); if (rc) return rc;
+    rc = launch_z<T, ZM_EXPORT>(h, z, 1, pb); if (rc) return rc;
   }
   return CHAN_OK;
 }

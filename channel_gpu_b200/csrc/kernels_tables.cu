@@ -90,21 +90,55 @@ static int perm_pos(const FftPlan& p, int n, int s) {   // where DIF leaves outp
   int r = p.radix[s - 1];
   return (n % r) * p.span[s - 1] + perm_pos(p, n / r, s - 1);
 }
-static int upload_inverse_perm(chan_handle* h, const FftPlan& p, int** dev) {
-  std::vector<int> inv(p.n);
-  for (int n = 0; n < p.n; n++) inv[perm_pos(p, n, p.nstage)] = n;
-  CHAN_CUDA(h, cudaMalloc(dev, sizeof(int) * p.n));
-  CHAN_CUDA(h, cudaMemcpy(*dev, inv.data(), sizeof(int) * p.n, cudaMemcpyHostToDevice));
+int perm_pos_of(const FftPlan& p, int n) { return perm_pos(p, n, p.nstage); }
+static int upload_perms(chan_handle* h, FftPlan& p, int** dinv, int** dpos) {
+  std::vector<int> inv(p.n), pos(p.n);
+  for (int n = 0; n < p.n; n++) { pos[n] = perm_pos(p, n, p.nstage); inv[pos[n]] = n; }
+  CHAN_CUDA(h, cudaMalloc(dinv, sizeof(int) * p.n));
+  CHAN_CUDA(h, cudaMalloc(dpos, sizeof(int) * p.n));
+  CHAN_CUDA(h, cudaMemcpy(*dinv, inv.data(), sizeof(int) * p.n, cudaMemcpyHostToDevice));
+  CHAN_CUDA(h, cudaMemcpy(*dpos, pos.data(), sizeof(int) * p.n, cudaMemcpyHostToDevice));
+  p.inv = *dinv; p.pos = *dpos;
   return CHAN_OK;
 }
 
-static void make_plan(FftPlan* p, int n) {
-  p->n = n; p->nstage = 0;
-  int m = n, span = 1;
-  while (m % 4 == 0) { p->radix[p->nstage] = 4; p->span[p->nstage++] = span; span *= 4; m /= 4; }
-  while (m % 2 == 0) { p->radix[p->nstage] = 2; p->span[p->nstage++] = span; span *= 2; m /= 2; }
-  while (m % 3 == 0) { p->radix[p->nstage] = 3; p->span[p->nstage++] = span; span *= 3; m /= 3; }
-  if (m != 1) p->n = -1;     // unsupported factor
+// Radix schedule: fewest stages (>= 2) out of {16,12,8,6,4,3,2}, then the largest smallest radix.
+// small_last: the last stage is fused with the pointwise product in z and must be 4, 3 or 2
+// (6 lines x r_L complex values live in registers).
+static int g_max_radix = 16;
+static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int* bestmin, bool small_last) {
+  static const int cand[7] = { 16, 12, 8, 6, 4, 3, 2 };
+  if (n == 1) {
+    if (depth != maxdepth) return false;
+    int mn = 99; bool has_small = false;
+    for (int i = 0; i < depth; i++) { mn = cur[i] < mn ? cur[i] : mn; if (cur[i] <= 4) has_small = true; }
+    if (small_last && !has_small) return false;
+    if (mn > *bestmin) { *bestmin = mn; for (int i = 0; i < depth; i++) best[i] = cur[i]; }
+    return true;
+  }
+  if (depth >= maxdepth) return false;
+  bool found = false;
+  for (int c = 0; c < 7; c++) {
+    int r = cand[c];
+    if (n % r || r > g_max_radix) continue;
+    if (depth > 0 && r > cur[depth - 1]) continue;      // non-increasing: each multiset once
+    cur[depth] = r;
+    if (plan_search(n / r, depth + 1, maxdepth, cur, best, bestmin, small_last)) found = true;
+  }
+  return found;
+}
+void make_plan(FftPlan* p, int n, bool small_last, int max_radix) {
+  g_max_radix = max_radix;
+  int cur[16], best[16], bestmin = 0, ns = 0;
+  for (int d = 2; d <= 12 && !ns; d++) { bestmin = 0; if (plan_search(n, 0, d, cur, best, &bestmin, small_last)) ns = d; }
+  p->n = ns ? n : -1; p->nstage = ns;
+  if (!ns) return;
+  if (small_last) {     // move the largest radix <= 4 to the end
+    int li = -1; for (int i = 0; i < ns; i++) if (best[i] <= 4 && (li < 0 || best[i] > best[li])) li = i;
+    int v = best[li]; for (int i = li; i + 1 < ns; i++) best[i] = best[i + 1]; best[ns - 1] = v;
+  }
+  int span = 1;
+  for (int i = 0; i < ns; i++) { p->radix[i] = best[i]; p->span[i] = span; span *= best[i]; }
 }
 
 template <typename T>
@@ -180,15 +214,15 @@ static int build_tables_t(chan_handle* h) {
     h->yt.d2[dir].rP = p + 5 * ny; h->yt.d2[dir].rN = p + 6 * ny;
     h->yt.d2[dir].wP = p + 7 * ny; h->yt.d2[dir].wC = p + 8 * ny; h->yt.d2[dir].wN = p + 9 * ny;
   }
-  make_plan(&h->px, h->d.nx);
-  make_plan(&h->pz, h->d.nzp);
+  make_plan(&h->px, h->d.nx, false, h->tune.max_radix);
+  make_plan(&h->pz, h->d.nzp, true, h->tune.max_radix);
   if (h->px.n < 0 || h->pz.n < 0)
     return set_err(h, CHAN_ERR_ARG, "NX=%d and 2NZ-2=%d must factor into 2s and 3s", h->d.nx, h->d.nzp);
   int rc = upload_twiddles<T>(h, h->d.nx, &h->tw_x); if (rc) return rc;
   rc = upload_twiddles<T>(h, h->d.nzp, &h->tw_z); if (rc) return rc;
   h->px.tw = h->tw_x; h->pz.tw = h->tw_z;
-  rc = upload_inverse_perm(h, h->px, &h->invx); if (rc) return rc;
-  rc = upload_inverse_perm(h, h->pz, &h->invz); if (rc) return rc;
+  rc = upload_perms(h, h->px, &h->invx, &h->posx); if (rc) return rc;
+  rc = upload_perms(h, h->pz, &h->invz, &h->posz); if (rc) return rc;
   return CHAN_OK;
 }
 

@@ -1,0 +1,246 @@
+// Phases of the plane-stage kernels (kernels_plane.cu), written as __host__ __device__ functions
+// of (tid, nthr) so tests/host/fft_host_test.cu can execute them on the CPU.
+//
+// Stage order.  Inverse transforms run DIT (digit-reversed in, natural out), forward transforms DIF
+// (natural in, digit-reversed out).  Consequences:
+//  * the m = 1 stage of an inverse transform is fused with the LOAD from global memory (the loader
+//    gathers the r_0 inputs of a group through inv[], builds zero padding / Hermitian extension on
+//    the fly, does the butterfly in registers and only then touches shared memory);
+//  * the m = 1 stage of a forward x-transform is fused with the STORE (truncation = which outputs
+//    are written);
+//  * in z, the last inverse stage, the pointwise product u x omega and the first forward stage
+//    share one pass: a thread holds all 6 lines of r_L positions k + q*m in registers.  These are
+//    the large-span stages, whose shared-memory accesses are contiguous across threads.
+// Physical space is in NATURAL order (x and z), so nothing downstream needs an index table.
+#pragma once
+#include "fft_core.cuh"
+#include "chan_internal.h"
+
+namespace chan {
+namespace fft {
+
+template <class T2> struct PlanT { int n, nstage; int radix[16], span[16]; const T2* tw; const int* inv; const int* pos; };
+
+template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
+  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage;
+  for (int i = 0; i < 16; i++) { q.radix[i] = p.radix[i]; q.span[i] = p.span[i]; }
+  q.tw = (const T2*)p.tw; q.inv = p.inv; q.pos = p.pos;
+  return q;
+}
+
+// =================================== x direction =================================================
+// shared layout: s[pos*TK + t], t = kz within the tile (batch-fastest: conflict-free at every stride)
+
+// inverse, stage 0 (m = 1) fused with the zero-padding load of the compact spectral rows
+template <class T2, int R>
+FFT_HD void x_inv_load_stage0(T2* s, const T2* src, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax, int tid, int nthr) {
+  const int n = pl.n, ng = n / R;
+  for (int b = tid; b < ng * TK; b += nthr) {
+    int t = b % TK, g = b / TK, kz = kz0 + t;
+    // all R loads are issued back to back (clamped address + select), never behind a branch
+    T2 a[R]; int ik[R];
+#pragma unroll
+    for (int q = 0; q < R; q++) {
+      int nq = FFT_LDG(pl.inv + g * R + q);
+      ik[q] = nq <= kxmax ? nq : (nq >= n - kxmax ? nq - n + Kx : -1);
+    }
+    const bool kz_ok = kz < Kz;
+#pragma unroll
+    for (int q = 0; q < R; q++) a[q] = src[(size_t)(ik[q] < 0 ? 0 : ik[q]) * Kz + (kz_ok ? kz : 0)];
+#pragma unroll
+    for (int q = 0; q < R; q++) if (ik[q] < 0 || !kz_ok) a[q] = mk2<T2>(0, 0);
+    Dft<R, +1, T2>::run(a);
+#pragma unroll
+    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * TK + t] = a[p];
+  }
+}
+// inverse, last stage fused with the store of the natural-order x line
+template <class T2, int R>
+FFT_HD void x_inv_last_store(const T2* s, T2* q, const PlanT<T2>& pl, int TK, int kz0, int Kz, int tid, int nthr) {
+  const int n = pl.n, m = n / R;
+  for (int b = tid; b < m * TK; b += nthr) {
+    int t = b % TK, k = b / TK, kz = kz0 + t;
+    T2 a[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) a[i] = s[(size_t)(k + i * m) * TK + t];
+    apply_twiddles<R, +1, T2>(a, pl.tw, k, 1);
+    Dft<R, +1, T2>::run(a);
+    if (kz < Kz) {
+#pragma unroll
+      for (int p = 0; p < R; p++) q[(size_t)(k + p * m) * Kz + kz] = a[p];
+    }
+  }
+}
+// forward, first stage (largest span) fused with the load of the natural-order x line
+template <class T2, int R>
+FFT_HD void x_fwd_load_first(T2* s, const T2* q, const PlanT<T2>& pl, int TK, int kz0, int Kz, int tid, int nthr) {
+  const int n = pl.n, m = n / R;
+  for (int b = tid; b < m * TK; b += nthr) {
+    int t = b % TK, k = b / TK, kz = kz0 + t;
+    T2 a[R];
+#pragma unroll
+    for (int p = 0; p < R; p++) a[p] = kz < Kz ? q[(size_t)(k + p * m) * Kz + kz] : mk2<T2>(0, 0);
+    Dft<R, -1, T2>::run(a);
+    apply_twiddles<R, -1, T2>(a, pl.tw, k, 1);
+#pragma unroll
+    for (int i = 0; i < R; i++) s[(size_t)(k + i * m) * TK + t] = a[i];
+  }
+}
+// forward, stage 0 (m = 1) fused with the truncating store into the compact spectral rows
+template <class T2, int R>
+FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax,
+                               typename RealOf<T2>::type scale, int tid, int nthr) {
+  const int n = pl.n, ng = n / R;
+  for (int b = tid; b < ng * TK; b += nthr) {
+    int t = b % TK, g = b / TK, kz = kz0 + t;
+    T2 a[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) a[i] = s[(size_t)(g * R + i) * TK + t];
+    Dft<R, -1, T2>::run(a);
+    if (kz < Kz) {
+#pragma unroll
+      for (int p = 0; p < R; p++) {
+        int np = FFT_LDG(pl.inv + g * R + p);
+        int ikx = np <= kxmax ? np : (np >= n - kxmax ? np - n + Kx : -1);
+        if (ikx >= 0) {
+          T2 v = a[p];
+          if (scale != 0) { v.x /= scale; v.y /= scale; }
+          dst[(size_t)ikx * Kz + kz] = v;
+        }
+      }
+    }
+  }
+}
+// one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
+template <class T2, int SIGN, bool DIT>
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int t, int st, int nlines, int nact, int nper, int tid, int nthr) {
+  int r = pl.radix[t], m = pl.span[t];
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, m, st, nlines, nact, nper, pl.tw, tid, nthr)));
+}
+
+// =================================== z direction =================================================
+// One block works on XP x-pairs; shared layout s[pos*ST + xpl*NIN + f], ST = XP*NIN.
+// Two-for-one: line (xpl, f) holds field f at x0 = 2*xp (real part) and x1 = 2*xp+1 (imaginary part).
+
+// value of the Hermitian-extended, zero-padded packed spectrum at natural index nz
+// index and kind of the Hermitian-extended, zero-padded packed spectrum at natural index nz:
+// kind 0 -> zero, 1 -> A + iB (A,B at k = nz), 2 -> conj(A) + i conj(B) (k = n - nz)
+FFT_HD void z_packed_index(int nz, int n, int Kz, int& k, int& kind) {
+  kind = nz < Kz ? 1 : (nz > n - Kz ? 2 : 0);
+  k = kind == 1 ? nz : (kind == 2 ? n - nz : 0);
+}
+template <class T2>
+FFT_HD T2 z_packed_combine(T2 A, T2 B, int k, int kind) {
+  typedef typename RealOf<T2>::type T;
+  if (kind == 0) return mk2<T2>(0, 0);
+  if (kind == 1 && k == 0) return mk2<T2>(A.x, B.x);            // imag of the kz=0 bin dropped, as C2R does
+  T sg = kind == 1 ? (T)1 : (T)-1;
+  return mk2<T2>(A.x - sg * B.y, sg * A.y + B.x);
+}
+
+// inverse, stage 0 fused with the packing load.  q0 -> Q[field 0][plane][x = 2*xp0][0]; fields are
+// fstride apart, x rows Kz apart.
+template <class T2, int R, int NIN>
+FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
+  const int n = pl.n, ng = n / R, ST = XP * NIN;
+  for (int b = tid; b < ng * ST; b += nthr) {
+    int li = b % ST, g = b / ST, f = li % NIN, xpl = li / NIN;
+    T2 a[R];
+    if (xpl < nxp_valid) {
+      const T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
+      // loads are issued in independent batches of <= 8 pairs (clamped address + select), never behind a branch
+      constexpr int HB = R > 8 ? 8 : R;
+#pragma unroll
+      for (int h0 = 0; h0 < R; h0 += HB) {
+        int kk[HB], kind[HB]; T2 B[HB];
+#pragma unroll
+        for (int i = 0; i < HB; i++) z_packed_index(FFT_LDG(pl.inv + g * R + h0 + i), n, Kz, kk[i], kind[i]);
+#pragma unroll
+        for (int i = 0; i < HB; i++) { a[h0 + i] = qa[kk[i]]; B[i] = qa[Kz + kk[i]]; }
+#pragma unroll
+        for (int i = 0; i < HB; i++) a[h0 + i] = z_packed_combine<T2>(a[h0 + i], B[i], kk[i], kind[i]);
+      }
+      Dft<R, +1, T2>::run(a);
+    } else {
+#pragma unroll
+      for (int i = 0; i < R; i++) a[i] = mk2<T2>(0, 0);
+    }
+#pragma unroll
+    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * SS + li] = a[p];
+  }
+}
+
+enum { ZM_ROTOR = 0, ZM_IDENTITY = 1, ZM_EXPORT = 2 };
+
+// last inverse stage + pointwise + first forward stage, all 'NIN' lines of one x-pair in registers.
+// umax3: per-thread running maxima of |u|,|v|,|w| (ROTOR).  phys0/phys1: output rows (EXPORT).
+template <class T2, int R, int MODE>
+FFT_HD void z_mid_fused(T2* s, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
+                        typename RealOf<T2>::type* umax3, typename RealOf<T2>::type* phys, size_t phys_xstride, int tid, int nthr) {
+  typedef typename RealOf<T2>::type T;
+  constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
+  constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
+  const int n = pl.n, m = n / R;
+  for (int b = tid; b < m * XP; b += nthr) {
+    int k = b % m, xpl = b / m;
+    if (xpl >= nxp_valid) continue;
+    T2 a[NIN][R];
+#pragma unroll
+    for (int f = 0; f < NIN; f++) {
+#pragma unroll
+      for (int i = 0; i < R; i++) a[f][i] = s[(size_t)(k + i * m) * SS + xpl * NIN + f];
+      apply_twiddles<R, +1, T2>(a[f], pl.tw, k, 1);
+      Dft<R, +1, T2>::run(a[f]);
+    }
+    if (MODE == ZM_EXPORT) {
+      T* o0 = phys + (size_t)(2 * xpl) * phys_xstride; T* o1 = o0 + phys_xstride;
+#pragma unroll
+      for (int p = 0; p < R; p++) { o0[k + p * m] = a[0][p].x; o1[k + p * m] = a[0][p].y; }
+      continue;
+    }
+    if (MODE == ZM_ROTOR) {
+      // rotorkernel (convolution_kernels.cu:107-131): every factor divided by N2, m = u x omega;
+      // .x is the point (x0, z), .y the point (x1, z).  Maxima are of the un-normalised velocities.
+#pragma unroll
+      for (int p = 0; p < R; p++) {
+        T2 u = a[0][p], v = a[1][p], w = a[2][p], ox = a[3][p], oy = a[4][p], oz = a[5][p];
+        umax3[0] = fmax(umax3[0], fmax(fabs(u.x), fabs(u.y)));
+        umax3[1] = fmax(umax3[1], fmax(fabs(v.x), fabs(v.y)));
+        umax3[2] = fmax(umax3[2], fmax(fabs(w.x), fabs(w.y)));
+        u.x /= n2; v.x /= n2; w.x /= n2; u.y /= n2; v.y /= n2; w.y /= n2;
+        ox.x /= n2; oy.x /= n2; oz.x /= n2; ox.y /= n2; oy.y /= n2; oz.y /= n2;
+        a[0][p] = mk2<T2>(v.x * oz.x - w.x * oy.x, v.y * oz.y - w.y * oy.y);
+        a[1][p] = mk2<T2>(w.x * ox.x - u.x * oz.x, w.y * ox.y - u.y * oz.y);
+        a[2][p] = mk2<T2>(u.x * oy.x - v.x * ox.x, u.y * oy.y - v.y * ox.y);
+      }
+    }
+#pragma unroll
+    for (int f = 0; f < NOUT; f++) {
+      Dft<R, -1, T2>::run(a[f]);
+      apply_twiddles<R, -1, T2>(a[f], pl.tw, k, 1);
+#pragma unroll
+      for (int i = 0; i < R; i++) s[(size_t)(k + i * m) * SS + xpl * NIN + f] = a[f][i];
+    }
+  }
+}
+
+// Hermitian unpacking of the two-for-one pair + truncation to kz < Kz, from the digit-reversed
+// output of the forward transform
+template <class T2, int NIN, int NOUT>
+FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
+  typedef typename RealOf<T2>::type T;
+  const int n = pl.n;
+  for (int b = tid; b < Kz * NOUT * XP; b += nthr) {
+    int k = b % Kz, l = b / Kz, f = l % NOUT, xpl = l / NOUT;
+    if (xpl >= nxp_valid) continue;
+    T2 Yk = s[(size_t)pl.pos[k] * SS + xpl * NIN + f];
+    T2 Yn = s[(size_t)pl.pos[k ? n - k : 0] * SS + xpl * NIN + f];
+    const T h = (T)0.5;
+    T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
+    qa[k] = mk2<T2>(h * (Yk.x + Yn.x), h * (Yk.y - Yn.y));
+    qa[Kz + k] = mk2<T2>(h * (Yk.y + Yn.y), h * (Yn.x - Yk.x));
+  }
+}
+
+}  // namespace fft
+}  // namespace chan
