@@ -203,18 +203,18 @@ def main():
     import torch
     import channel_gpu_b200 as cg
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    comm = None
+    torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
+        from channel_gpu_b200 import nccl_boot
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
+        comm = nccl_boot.init_comm(rank, world, local)
     W = max(3, args.warmup); K = args.steps
     nx, ny, nz = cfg["nx"], cfg["ny"], cfg["nz"]
     prec = args.precision
     cplx = np.complex128 if prec == 8 else np.complex64
     sz = sizes(cfg, prec)
-
-    if world > 1:
-        raise SystemExit("multi-GPU bench not wired yet")
 
     ddv, g, um = synthetic_fields(nx, ny, nz, cplx)
     # pinned host staging for the end-to-end leg
@@ -224,7 +224,7 @@ def main():
     ddv_t, ddv_p = pinned(ddv); g_t, g_p = pinned(g)
     out_ddv_t = torch.empty_like(ddv_t).pin_memory(); out_g_t = torch.empty_like(g_t).pin_memory()
 
-    ch = cg.Channel(nx, ny, nz, precision=prec, device=local, plane_batch=args.plane_batch)
+    ch = cg.Channel(nx, ny, nz, precision=prec, device=local, plane_batch=args.plane_batch, rank=rank, size=world, nccl_comm=comm)
     ch.set_fields(ddv_p, g_p); ch.set_umean(um)
     ch.rk_init()
     ch.rk_step(W); ch.sync()
@@ -234,11 +234,17 @@ def main():
     ch.set_timing(True); ch.stage_ms()
     l0 = ch.launch_count()
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     t0 = time.perf_counter()
     ch.rk_step(K)
     ch.sync()
     wall = time.perf_counter() - t0
     ms, cnt = ch.stage_ms()
+    if world > 1:      # max over ranks of the device-timed step
+        t = torch.tensor([ms[4], wall], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms[4] = float(t[0]); wall = float(t[1])
     launches = ch.launch_count() - l0
     ch.set_timing(False)
     clk = clocks.stop()
@@ -249,6 +255,10 @@ def main():
 
     # ---- end to end through the public API with host buffers ----------------------------
     if args.profile:
+        if rank == 0:
+            print(json.dumps({"profile_run": True, "n_gpus": world, "ms_per_step": step_ms, "stage_ms": ms, "launches": launches}))
+        return
+    if False:
         print(json.dumps({"profile_run": True, "ms_per_step": step_ms, "stage_ms": ms, "launches": launches}))
         return
     ch2 = ch
@@ -291,9 +301,21 @@ def main():
                       "l2": "working set per step (>1 GB) exceeds the 126 MB L2; no flush needed", "finite": finite},
            "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "stages": stages,
            "wall_ms_per_step": 1e3 * wall / K}
-    if not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline_sample(cfg, prec)
-    print(json.dumps(out))
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["e2e"]["value"] = K / float(t[0])
+        S = world
+        out["nvlink"] = {"bytes_per_gpu_per_step_each_way": int(3 * 9 * (P / S) * (S - 1) / S),
+                         "note": "9 field exchanges per substep, active modes only, NCCL grouped send/recv on the compute stream (not yet overlapped)"}
+    if rank == 0:
+        if not args.no_cpu_baseline and world == 1:
+            out["cpu_baseline"] = cpu_baseline_sample(cfg, prec)
+        print(json.dumps(out))
+    if world > 1:
+        ch.close()
+        nccl_boot.destroy_comm(comm)
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -24,7 +24,8 @@ class ChannelError(RuntimeError):
 class _Config(C.Structure):
     _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("nz", C.c_int), ("precision", C.c_int),
                 ("reynolds", C.c_double), ("qvelocity", C.c_double), ("cfl", C.c_double),
-                ("rank", C.c_int), ("size", C.c_int), ("device", C.c_int), ("plane_batch", C.c_int)]
+                ("rank", C.c_int), ("size", C.c_int), ("device", C.c_int), ("plane_batch", C.c_int),
+                ("nccl_comm", C.c_void_p)]
 
 
 class _Scalars(C.Structure):
@@ -90,13 +91,16 @@ def partition(n, size, rank):
 class Channel:
     """One GPU's time-stepper.  setUp + setRK3 + setRKmean (setUp.c:3, RK3.c:17, meanUevol.c:43)."""
 
-    def __init__(self, nx, ny, nz, precision=8, reynolds=3250.0, qvelocity=1.8, cfl=0.5, device=-1, plane_batch=0):
+    def __init__(self, nx, ny, nz, precision=8, reynolds=3250.0, qvelocity=1.8, cfl=0.5, device=-1, plane_batch=0,
+                 rank=0, size=1, nccl_comm=None):
         self.L = load_library()
         cfg = _Config()
         self.L.chan_config_default(C.byref(cfg))
         cfg.nx, cfg.ny, cfg.nz, cfg.precision = nx, ny, nz, precision
         cfg.reynolds, cfg.qvelocity, cfg.cfl = reynolds, qvelocity, cfl
         cfg.device, cfg.plane_batch = device, plane_batch
+        cfg.rank, cfg.size, cfg.nccl_comm = rank, size, nccl_comm
+        self.rank, self.size = rank, size
         self.nx, self.ny, self.nz, self.precision = nx, ny, nz, precision
         self.cplx = np.complex64 if precision == 4 else np.complex128
         self.real = np.float32 if precision == 4 else np.float64

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libchannel_b200.so")
-SOURCES = ["api.cu", "kernels_tables.cu", "kernels_pencil.cu", "kernels_plane.cu", "kernels_misc.cu", "kernels_static.cu"]
+SOURCES = ["api.cu", "kernels_tables.cu", "kernels_pencil.cu", "kernels_plane.cu", "kernels_misc.cu", "kernels_static.cu", "comm.cu"]
 NVCC = os.environ.get("NVCC", "nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC"]
@@ -49,7 +49,7 @@ def build_lib(force=False, verbose=False):
         for l in logs:
             sys.stderr.write(l)
     if jobs or not os.path.exists(LIB):
-        run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs)
+        run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-lnccl"])
     return LIB
 
 

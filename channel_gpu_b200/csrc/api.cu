@@ -51,7 +51,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   h->cfg = *cfg;
   if (cfg->precision != 4 && cfg->precision != 8) return set_err(h, CHAN_ERR_ARG, "precision must be 4 or 8, got %d", cfg->precision);
   if (cfg->nx < 8 || cfg->ny < 8 || cfg->nz < 5 || (cfg->nx & 1)) return set_err(h, CHAN_ERR_ARG, "grid %dx%dx%d: need even NX>=8, NY>=8, NZ>=5", cfg->nx, cfg->ny, cfg->nz);
-  if (cfg->size != 1 || cfg->rank != 0) return set_err(h, CHAN_ERR_ARG, "this build runs one slab per handle; multi-GPU runs go through the python launcher");
+  if (cfg->size < 1 || cfg->size > 8 || cfg->rank < 0 || cfg->rank >= cfg->size) return set_err(h, CHAN_ERR_ARG, "rank %d of %d: 1..8 ranks (one NVSwitch box) are supported", cfg->rank, cfg->size);
+  if (cfg->size > 1 && !cfg->nccl_comm) return set_err(h, CHAN_ERR_ARG, "size > 1 needs chan_config.nccl_comm");
+  h->nccl_comm = cfg->nccl_comm;
   h->prec = cfg->precision;
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
@@ -63,7 +65,24 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   d.nx = cfg->nx; d.ny = cfg->ny; d.nz = cfg->nz; d.nzp = 2 * cfg->nz - 2;
   d.kxmax = d.nx / 3; d.Kx = 2 * d.kxmax + 1; d.Kz = d.nzp / 3 + 1;          // dealias.cu:37 (integer divisions)
   if (d.Kz > d.nz - 1 || d.kxmax >= d.nx / 2) return set_err(h, CHAN_ERR_ARG, "grid too small for the 2/3 rule");
-  d.ikx0 = 0; d.Kxl = d.Kx; d.j0 = 0; d.nyl = d.ny; d.M = (long)d.Kxl * d.Kz;
+  // slabs: active kx for the pencil stages, y planes for the plane stage (main.c:47, channel.h:71-79),
+  // split as evenly as possible — no divisibility requirement
+  for (int r = 0; r <= cfg->size; r++) {
+    int s0 = d.Kx, c0 = 0, s1 = d.ny, c1 = 0;
+    if (r < cfg->size) { chan_partition(d.Kx, cfg->size, r, &s0, &c0); chan_partition(d.ny, cfg->size, r, &s1, &c1); }
+    h->part_kx[r] = s0; h->part_j[r] = s1;
+  }
+  d.ikx0 = h->part_kx[cfg->rank]; d.Kxl = h->part_kx[cfg->rank + 1] - d.ikx0;
+  d.j0 = h->part_j[cfg->rank]; d.nyl = h->part_j[cfg->rank + 1] - d.j0;
+  d.M = (long)d.Kxl * d.Kz;
+  if (d.Kxl < 1 || d.nyl < 1) return set_err(h, CHAN_ERR_ARG, "grid too small for %d ranks", cfg->size);
+  h->seg.nseg = cfg->size;
+  { long off = 0;
+    for (int r = 0; r < cfg->size; r++) {
+      h->seg.start[r] = h->part_kx[r]; h->seg.width[r] = h->part_kx[r + 1] - h->part_kx[r];
+      h->seg.base[r] = off; off += (long)d.nyl * h->seg.width[r] * d.Kz;
+    }
+    h->seg.start[cfg->size] = d.Kx; }
   if (cfg->device >= 0) CHAN_CUDA(h, cudaSetDevice(cfg->device));
   CHAN_CUDA(h, cudaGetDevice(&h->device));
   CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -85,6 +104,11 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (pb > d.nyl) pb = d.nyl;
   h->plane_batch = pb;
   if ((rc = alloc_dev(h, &h->Q, plane_q * pb))) return rc;
+  if (cfg->size > 1) {
+    const size_t pb_bytes = (size_t)d.nyl * d.Kx * d.Kz * csize(h);
+    for (int f = 0; f < 6; f++) if ((rc = alloc_dev(h, &h->rcv[f], pb_bytes))) return rc;
+    for (int f = 0; f < 3; f++) if ((rc = alloc_dev(h, &h->snd[f], pb_bytes))) return rc;
+  }
   const size_t rb = (size_t)d.ny * h->prec;
   if ((rc = alloc_dev(h, &h->mean_u, rb))) return rc;
   if ((rc = alloc_dev(h, &h->mean_N, rb))) return rc;
@@ -103,7 +127,8 @@ extern "C" void chan_destroy(chan_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
                    h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
-                   h->mean_uw, h->mean_tmp, h->sc, h->io_buf };
+                   h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
+                   h->snd[0], h->snd[1], h->snd[2] };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -270,6 +295,7 @@ extern "C" int chan_statistics(chan_handle* h, double* out) {
   double* d; const size_t b = sizeof(double) * 4 * h->d.ny;
   CHAN_CUDA(h, cudaMalloc(&d, b));
   int rc = launch_stats(h, d);
+  if (!rc) rc = allreduce_sum_host(h, d, 4 * h->d.ny);
   if (!rc) { cudaError_t e = cudaMemcpyAsync(out, d, b, cudaMemcpyDeviceToHost, h->stream); if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) rc = set_err(h, CHAN_ERR_CUDA, "statistics copy: %s", cudaGetErrorString(e)); }
   cudaFree(d);

@@ -52,6 +52,12 @@ struct FftPlan {
   const int* pos;               // natural index -> digit-reversed position
 };
 
+// Plane-side addressing of one compact field whose rows come from several kx slabs (multi-GPU: one
+// segment per source rank, as received; single GPU: one segment = the field itself).  Element
+// (row jl, ikx, kz) of segment s = start[s] <= ikx < start[s+1] lives at
+//   base[s] + (jl*width[s] + ikx - start[s])*Kz + kz      (in complex elements)
+struct SegMap { int nseg; int start[9]; int width[8]; long base[8]; };
+
 // ---- handle ---------------------------------------------------------------
 struct Dims {
   int nx, ny, nz, nzp;          // NZ = complex z count, nzp = 2NZ-2 physical z points
@@ -95,6 +101,11 @@ struct chan_handle {
   void *mean_a, *mean_b;        // host-mesh differences in T (meanUevol.c:230-231)
   void *mean_u, *mean_N, *mean_uw, *mean_tmp;   // T[NY] (+ scratch)
   chan::Scalars* sc;            // device
+  // multi-GPU exchange (comm.cu): NCCL communicator owned by the caller, receive buffers of the 6
+  // fields entering the plane stage, send buffers of the 3 leaving it, slab boundaries of all ranks
+  void* nccl_comm; void* rcv[6]; void* snd[3];
+  int part_kx[9], part_j[9];      // part_kx[r] = first active-kx index of rank r (part_kx[size] = Kx), same for planes
+  chan::SegMap seg;               // plane-side segmentation (identical for every field)
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;
   struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
@@ -128,5 +139,10 @@ int launch_pack(chan_handle* h, const void* ref_layout_dev, void* compact);     
 int launch_unpack(chan_handle* h, const void* compact, void* ref_layout_dev);    // [j][m] -> [i][k][j] (zeros outside)
 int launch_scalar_stage(chan_handle* h, int n);              // mean flow, dt, bookkeeping
 int launch_end_step(chan_handle* h);
+// comm.cu
+int exchange_to_planes(chan_handle* h, int nf, void* const* pencil_fields);      // -> h->rcv[0..nf)
+int exchange_to_pencils(chan_handle* h, int nf, void* const* pencil_fields);     // h->snd[0..nf) ->
+int allreduce_umax(chan_handle* h);
+int allreduce_sum_host(chan_handle* h, double* dev_buf, int n);
 int launch_stats(chan_handle* h, double* out4ny_dev);
 }  // namespace chan

@@ -29,7 +29,8 @@ using namespace fft;
 template <typename T>
 struct XArgs {
   typedef typename Vec2<T>::type T2;
-  const T2* src[6]; T2* dst[6];   // compact plane-major fields
+  const T2* src[6]; T2* dst[6];   // plane-side field buffers (see SegMap)
+  SegMap seg; int j_glob0;        // global index of local plane 0 (export only)
   T2* Q;                          // [f][pb][NX][Kz]
   FftPlan px;
   int nx, Kx, Kz, kxmax, j_start, pb; long M;
@@ -48,9 +49,9 @@ __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   const int kz0 = blockIdx.x * TK, jb = blockIdx.y, f = blockIdx.z;
   if (a.dbg_skip & 1) return;
   const PlanT<T2> pl = plan_of<T2>(a.px);
-  const T2* src = a.src[f] + (size_t)(a.j_start + jb) * a.M;
+  const T2* src = a.src[f];
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s, src, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
   __syncthreads();
   for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
   FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
@@ -66,11 +67,11 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   if (a.dbg_skip & 2) return;
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  T2* dst = a.dst[f] + (size_t)(a.j_start + jb) * a.M;
+  T2* dst = a.dst[f];
   FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
   for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, dst, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, dst, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
 // -------------------------------------------------------------------------------
@@ -82,7 +83,7 @@ struct ZArgs {
   int nx, nzp, Kz, pb, j_start, XP, SS;   // SS: shared-memory elements per position (>= XP*NIN)
   T n2;                            // (T)N2: the reference divides by the int N2 (convolution_kernels.cu:107-121)
   unsigned long long* umax_bits;   // 3 slots
-  T* phys; int nz;                 // export only: real [NY][NX][2NZ]
+  T* phys; int nz, j_glob0;        // export only: real [NY][NX][2NZ]
 };
 
 __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double v) {
@@ -111,7 +112,7 @@ __global__ void __launch_bounds__(256, 2) zstage_kernel(ZArgs<T> a) {
   if (a.dbg_stop == 2) return;
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
-  if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
+  if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
   switch (pl.radix[pl.nstage - 1]) {
     case 2: z_mid_fused<T2, 2, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
     case 3: z_mid_fused<T2, 3, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
@@ -198,7 +199,7 @@ template <typename T>
 static void fill_x(chan_handle* h, XArgs<T>& a) {
   typedef typename Vec2<T>::type T2;
   a.Q = (T2*)h->Q; a.px = h->px; a.nx = h->d.nx; a.Kx = h->d.Kx; a.Kz = h->d.Kz; a.kxmax = h->d.kxmax;
-  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0; a.dbg_skip = h->tune.x_skip;
+  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0; a.dbg_skip = h->tune.x_skip; a.seg = h->seg; a.j_glob0 = h->d.j0;
 }
 template <typename T>
 static void fill_z(chan_handle* h, ZArgs<T>& a) {
@@ -206,24 +207,30 @@ static void fill_z(chan_handle* h, ZArgs<T>& a) {
   a.Q = (T2*)h->Q; a.pz = h->pz; a.nx = h->d.nx; a.nzp = h->d.nzp; a.Kz = h->d.Kz; a.nz = h->d.nz;
   a.n2 = (T)(h->d.nx * h->d.nzp);
   a.umax_bits = h->sc->umax_bits;
-  a.phys = 0; a.XP = 1; a.SS = 0; a.dbg_stop = h->tune.z_stop;
+  a.phys = 0; a.XP = 1; a.SS = 0; a.dbg_stop = h->tune.z_stop; a.j_glob0 = h->d.j0;
 }
 
 template <typename T>
 static int nonlinear_t(chan_handle* h) {
   typedef typename Vec2<T>::type T2;
   XArgs<T> xi, xf; fill_x(h, xi); fill_x(h, xf);
-  const void* in[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
-  void* out[3] = { h->ox, h->oy, h->oz };
+  void* pin[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
+  void* pout[3] = { h->ox, h->oy, h->oz };
+  const bool multi = h->cfg.size > 1;
+  if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
+  const void* in[6]; void* out[3];
+  for (int f = 0; f < 6; f++) in[f] = multi ? h->rcv[f] : pin[f];
+  for (int f = 0; f < 3; f++) out[f] = multi ? h->snd[f] : pout[f];
   for (int f = 0; f < 6; f++) { xi.src[f] = (const T2*)in[f]; xi.dst[f] = 0; xf.src[f] = 0; xf.dst[f] = f < 3 ? (T2*)out[f] : 0; }
   ZArgs<T> z; fill_z(h, z);
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
-    xi.j_start = xf.j_start = z.j_start = h->d.j0 + js; xi.pb = xf.pb = z.pb = pb;
+    xi.j_start = xf.j_start = z.j_start = js; xi.pb = xf.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 6, pb); if (rc) return rc;
     rc = launch_z<T, ZM_ROTOR>(h, z, 6, pb); if (rc) return rc;
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
   }
+  if (multi) { int rc = allreduce_umax(h); if (rc) return rc; rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
   return CHAN_OK;
 }
 
@@ -232,29 +239,35 @@ static int symmetrize_t(chan_handle* h, void* fa, void* fb) {
   typedef typename Vec2<T>::type T2;
   XArgs<T> xi, xf; fill_x(h, xi); fill_x(h, xf);
   for (int f = 0; f < 6; f++) { xi.src[f] = 0; xi.dst[f] = 0; xf.src[f] = 0; xf.dst[f] = 0; }
-  xi.src[0] = (const T2*)fa; xi.src[1] = (const T2*)fb; xf.dst[0] = (T2*)fa; xf.dst[1] = (T2*)fb;
+  void* pf[2] = { fa, fb };
+  const bool multi = h->cfg.size > 1;
+  if (multi) { int rc = exchange_to_planes(h, 2, pf); if (rc) return rc; }
+  xi.src[0] = (const T2*)(multi ? h->rcv[0] : fa); xi.src[1] = (const T2*)(multi ? h->rcv[1] : fb);
+  xf.dst[0] = (T2*)(multi ? h->snd[0] : fa); xf.dst[1] = (T2*)(multi ? h->snd[1] : fb);
   xf.scale = (T)(h->d.nx * h->d.nzp);
   ZArgs<T> z; fill_z(h, z);
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
-    xi.j_start = xf.j_start = z.j_start = h->d.j0 + js; xi.pb = xf.pb = z.pb = pb;
+    xi.j_start = xf.j_start = z.j_start = js; xi.pb = xf.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 2, pb); if (rc) return rc;
     rc = launch_z<T, ZM_IDENTITY>(h, z, 2, pb); if (rc) return rc;
     rc = launch_x_any<T>(h, false, xf, 2, pb); if (rc) return rc;
   }
+  if (multi) { int rc = exchange_to_pencils(h, 2, pf); if (rc) return rc; }
   return CHAN_OK;
 }
 
 template <typename T>
 static int export_t(chan_handle* h, const void* f, void* phys) {
   typedef typename Vec2<T>::type T2;
+  if (h->cfg.size > 1) return set_err(h, CHAN_ERR_STATE, "chan_fft_backward_transpose is a single-GPU validation entry point");
   XArgs<T> xi; fill_x(h, xi);
   for (int k = 0; k < 6; k++) { xi.src[k] = 0; xi.dst[k] = 0; }
   xi.src[0] = (const T2*)f;
   ZArgs<T> z; fill_z(h, z); z.phys = (T*)phys;
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
-    xi.j_start = z.j_start = h->d.j0 + js; xi.pb = z.pb = pb;
+    xi.j_start = z.j_start = js; xi.pb = z.pb = pb;
     int rc = launch_x_any<T>(h, true, xi, 1, pb); if (rc) return rc;
     rc = launch_z<T, ZM_EXPORT>(h, z, 1, pb); if (rc) return rc;
   }

@@ -28,12 +28,19 @@ template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
   return q;
 }
 
+FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz) {
+  int sg = 0;
+#pragma unroll
+  for (int i = 1; i < 8; i++) sg += (i < sm.nseg && ikx >= sm.start[i]) ? 1 : 0;
+  return (size_t)sm.base[sg] + ((size_t)jl * sm.width[sg] + (ikx - sm.start[sg])) * Kz;
+}
+
 // =================================== x direction =================================================
 // shared layout: s[pos*TK + t], t = kz within the tile (batch-fastest: conflict-free at every stride)
 
 // inverse, stage 0 (m = 1) fused with the zero-padding load of the compact spectral rows
 template <class T2, int R>
-FFT_HD void x_inv_load_stage0(T2* s, const T2* src, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax, int tid, int nthr) {
+FFT_HD void x_inv_load_stage0(T2* s, const T2* src, const SegMap& sm, int jl, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax, int tid, int nthr) {
   const int n = pl.n, ng = n / R;
   for (int b = tid; b < ng * TK; b += nthr) {
     int t = b % TK, g = b / TK, kz = kz0 + t;
@@ -46,7 +53,7 @@ FFT_HD void x_inv_load_stage0(T2* s, const T2* src, const PlanT<T2>& pl, int TK,
     }
     const bool kz_ok = kz < Kz;
 #pragma unroll
-    for (int q = 0; q < R; q++) a[q] = src[(size_t)(ik[q] < 0 ? 0 : ik[q]) * Kz + (kz_ok ? kz : 0)];
+    for (int q = 0; q < R; q++) a[q] = src[seg_offset(sm, jl, ik[q] < 0 ? 0 : ik[q], Kz) + (kz_ok ? kz : 0)];
 #pragma unroll
     for (int q = 0; q < R; q++) if (ik[q] < 0 || !kz_ok) a[q] = mk2<T2>(0, 0);
     Dft<R, +1, T2>::run(a);
@@ -88,7 +95,7 @@ FFT_HD void x_fwd_load_first(T2* s, const T2* q, const PlanT<T2>& pl, int TK, in
 }
 // forward, stage 0 (m = 1) fused with the truncating store into the compact spectral rows
 template <class T2, int R>
-FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax,
+FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const SegMap& sm, int jl, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax,
                                typename RealOf<T2>::type scale, int tid, int nthr) {
   const int n = pl.n, ng = n / R;
   for (int b = tid; b < ng * TK; b += nthr) {
@@ -105,7 +112,7 @@ FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const PlanT<T2>& pl, int TK
         if (ikx >= 0) {
           T2 v = a[p];
           if (scale != 0) { v.x /= scale; v.y /= scale; }
-          dst[(size_t)ikx * Kz + kz] = v;
+          dst[seg_offset(sm, jl, ikx, Kz) + kz] = v;
         }
       }
     }
@@ -149,7 +156,7 @@ FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T
     if (xpl < nxp_valid) {
       const T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
       // loads are issued in independent batches of <= 8 pairs (clamped address + select), never behind a branch
-      constexpr int HB = R > 8 ? 8 : R;
+      constexpr int HB = R == 16 ? 8 : (R == 12 ? 6 : R);
 #pragma unroll
       for (int h0 = 0; h0 < R; h0 += HB) {
         int kk[HB], kind[HB]; T2 B[HB];

@@ -54,6 +54,8 @@ typedef struct chan_config {
   int rank, size;        /* domain_t.rank/size: slab of a multi-GPU run           */
   int device;            /* CUDA device ordinal, -1 = current (main.c:87)         */
   int plane_batch;       /* y-planes per FFT-stage launch group, 0 = auto         */
+  void* nccl_comm;       /* ncclComm_t of the `size` ranks (one per GPU of the box);
+                            NULL when size == 1.  Replaces MPI_COMM_WORLD (main.c:25-29) */
 } chan_config;
 
 typedef struct chan_scalars {

@@ -33,17 +33,22 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   Host<T2> H; H.build(nx, false);
   PlanT<T2> pl = plan_of<T2>(H.p);
   int kxmax = nx / 3, Kx = 2 * kxmax + 1;
-  std::vector<T2> src((size_t)Kx * Kz), q((size_t)nx * Kz), dst((size_t)Kx * Kz), s((size_t)nx * TK);
+  // two kx segments, as a 2-rank plane stage sees its receive buffer: rows of both at plane jl = 1
+  SegMap sm; sm.nseg = 2; int w0 = Kx / 2 + 1, w1 = Kx - w0;
+  sm.start[0] = 0; sm.start[1] = w0; sm.start[2] = Kx; sm.width[0] = w0; sm.width[1] = w1; sm.base[0] = 0; sm.base[1] = (long)3 * w0 * Kz;
+  const int jl = 1; const size_t segtot = (size_t)3 * Kx * Kz;
+  auto at = [&](int i, int kz) { return seg_offset(sm, jl, i, Kz) + kz; };
+  std::vector<T2> src(segtot), q((size_t)nx * Kz), dst(segtot), s((size_t)nx * TK);
   for (auto& v : src) { v.x = (T)frand(); v.y = (T)frand(); }
   double err = 0, nrm = 0;
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s.data(), src.data(), pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
     for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, t, TK, TK, TK, TK, tid, NTHR);
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
   }
   for (int kz = 0; kz < Kz; kz++) for (int x = 0; x < nx; x++) {
     cd acc = 0;
-    for (int i = 0; i < Kx; i++) { int kx = i <= kxmax ? i : i - Kx; acc += cd(src[(size_t)i * Kz + kz].x, src[(size_t)i * Kz + kz].y) * std::polar(1.0, 2 * PI * kx * x / nx); }
+    for (int i = 0; i < Kx; i++) { int kx = i <= kxmax ? i : i - Kx; acc += cd(src[at(i, kz)].x, src[at(i, kz)].y) * std::polar(1.0, 2 * PI * kx * x / nx); }
     cd got(q[(size_t)x * Kz + kz].x, q[(size_t)x * Kz + kz].y);
     err += std::norm(got - acc); nrm += std::norm(acc);
   }
@@ -52,10 +57,10 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
     for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, t, TK, TK, TK, TK, tid, NTHR);
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s.data(), dst.data(), pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s.data(), dst.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
   }
   err = nrm = 0;
-  for (size_t i = 0; i < src.size(); i++) { err += std::norm(cd(dst[i].x - src[i].x, dst[i].y - src[i].y)); nrm += std::norm(cd(src[i].x, src[i].y)); }
+  for (int i = 0; i < Kx; i++) for (int kz = 0; kz < Kz; kz++) { size_t o = at(i, kz); err += std::norm(cd(dst[o].x - src[o].x, dst[o].y - src[o].y)); nrm += std::norm(cd(src[o].x, src[o].y)); }
   double e2 = sqrt(err / nrm);
   printf("  x n=%4d plan", nx); for (int i = 0; i < pl.nstage; i++) printf(" %d", pl.radix[i]);
   printf("  inv err %.2e  roundtrip err %.2e\n", e1, e2);
