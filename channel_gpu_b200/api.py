@@ -67,6 +67,7 @@ def load_library():
         "chan_deriv_y_pencils_static": [vp, vp, C.c_long],
         "chan_partition": [ci, ci, ci, C.POINTER(ci), C.POINTER(ci)],
         "chan_active_kx": [ci], "chan_active_kz": [ci],
+        "chan_exchange_layout": [ci, ci, ci, ci, ci, ci, C.POINTER(C.c_long)],
     }
     for name, args in sig.items():
         f = getattr(L, name)
@@ -86,6 +87,16 @@ def partition(n, size, rank):
     if L.chan_partition(n, size, rank, C.byref(s), C.byref(c)):
         raise ChannelError("bad partition arguments")
     return s.value, c.value
+
+
+def exchange_layout(nx, ny, nz, size, rank, peer):
+    """chan_exchange_layout as a dict (complex-element offsets/counts of one field's exchange with `peer`)."""
+    L = load_library()
+    out = (C.c_long * 8)()
+    if L.chan_exchange_layout(nx, ny, nz, size, rank, peer, out):
+        raise ChannelError("bad exchange_layout arguments")
+    k = ("send_off", "send_cnt", "recv_off", "recv_cnt", "peer_kx0", "peer_kxl", "peer_j0", "peer_nyl")
+    return dict(zip(k, [int(v) for v in out]))
 
 
 class Channel:

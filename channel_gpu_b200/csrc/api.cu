@@ -25,6 +25,21 @@ extern "C" int chan_partition(int n, int size, int rank, int* start, int* count)
 extern "C" int chan_active_kx(int nx) { return 2 * (nx / 3) + 1; }
 extern "C" int chan_active_kz(int nz) { return (2 * nz - 2) / 3 + 1; }
 
+extern "C" int chan_exchange_layout(int nx, int ny, int nz, int size, int rank, int peer, long* out) {
+  if (!out || size < 1 || rank < 0 || rank >= size || peer < 0 || peer >= size) return CHAN_ERR_ARG;
+  const int Kx = chan_active_kx(nx), Kz = chan_active_kz(nz);
+  int kx0, kxl, j0, nyl, pkx0, pkxl, pj0, pnyl;
+  chan_partition(Kx, size, rank, &kx0, &kxl); chan_partition(ny, size, rank, &j0, &nyl);
+  chan_partition(Kx, size, peer, &pkx0, &pkxl); chan_partition(ny, size, peer, &pj0, &pnyl);
+  const long M = (long)kxl * Kz;
+  out[0] = (long)pj0 * M; out[1] = (long)pnyl * M;                 // my rows of the peer's planes: contiguous
+  long off = 0;                                                    // blocks of lower-ranked sources come first
+  for (int r = 0; r < peer; r++) { int s, c; chan_partition(Kx, size, r, &s, &c); off += (long)nyl * c * Kz; }
+  out[2] = off; out[3] = (long)nyl * pkxl * Kz;
+  out[4] = pkx0; out[5] = pkxl; out[6] = pj0; out[7] = pnyl;
+  return CHAN_OK;
+}
+
 extern "C" int chan_config_default(chan_config* c) {
   if (!c) return CHAN_ERR_ARG;
   memset(c, 0, sizeof(*c));

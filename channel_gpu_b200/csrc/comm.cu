@@ -20,20 +20,18 @@ namespace chan {
 static ncclDataType_t real_type(const chan_handle* h) { return h->prec == 4 ? ncclFloat : ncclDouble; }
 
 // pencil fields -> h->rcv[f]: peer p receives my rows [j0_p, j0_p + nyl_p) of every field
-int exchange_to_planes(chan_handle* h, int nf, void* const* fields) {
+static int exchange(chan_handle* h, int nf, void* const* pencil, void* const* plane, bool to_planes) {
   ncclComm_t comm = (ncclComm_t)h->nccl_comm;
   const int S = h->cfg.size, me = h->cfg.rank;
-  const size_t cb = 2 * (size_t)h->prec, Kz = h->d.Kz;
-  const size_t nyl = h->d.nyl;
+  const size_t cb = 2 * (size_t)h->prec;
   for (int f = 0; f < nf; f++) {
     CHAN_NCCL(h, ncclGroupStart());
     for (int p = 0; p < S; p++) {
-      size_t rows_p = h->part_j[p + 1] - h->part_j[p];
-      const char* sbuf = (const char*)fields[f] + (size_t)h->part_j[p] * h->d.M * cb;
-      size_t scount = rows_p * h->d.M * 2;
-      size_t kxl_p = h->part_kx[p + 1] - h->part_kx[p];
-      char* rbuf = (char*)h->rcv[f] + (size_t)h->seg.base[p] * cb;
-      size_t rcount = nyl * kxl_p * Kz * 2;
+      long L[8];
+      chan_exchange_layout(h->d.nx, h->d.ny, h->d.nz, S, me, p, L);   // the layout the CPU tests check
+      char* pen = (char*)pencil[f] + (size_t)L[0] * cb; char* pla = (char*)plane[f] + (size_t)L[2] * cb;
+      const char* sbuf = to_planes ? pen : pla; char* rbuf = to_planes ? pla : pen;
+      size_t scount = (size_t)(to_planes ? L[1] : L[3]) * 2, rcount = (size_t)(to_planes ? L[3] : L[1]) * 2;
       if (p == me) { CHAN_CUDA(h, cudaMemcpyAsync(rbuf, sbuf, scount * h->prec, cudaMemcpyDeviceToDevice, h->stream)); continue; }
       CHAN_NCCL(h, ncclSend(sbuf, scount, real_type(h), p, comm, h->stream));
       CHAN_NCCL(h, ncclRecv(rbuf, rcount, real_type(h), p, comm, h->stream));
@@ -42,30 +40,10 @@ int exchange_to_planes(chan_handle* h, int nf, void* const* fields) {
   }
   return CHAN_OK;
 }
-
+// pencil fields -> h->rcv[f]: peer p receives my rows [j0_p, j0_p + nyl_p) of every field
+int exchange_to_planes(chan_handle* h, int nf, void* const* fields) { return exchange(h, nf, fields, h->rcv, true); }
 // h->snd[f] -> pencil fields: the mirror image
-int exchange_to_pencils(chan_handle* h, int nf, void* const* fields) {
-  ncclComm_t comm = (ncclComm_t)h->nccl_comm;
-  const int S = h->cfg.size, me = h->cfg.rank;
-  const size_t cb = 2 * (size_t)h->prec, Kz = h->d.Kz;
-  const size_t nyl = h->d.nyl;
-  for (int f = 0; f < nf; f++) {
-    CHAN_NCCL(h, ncclGroupStart());
-    for (int p = 0; p < S; p++) {
-      size_t kxl_p = h->part_kx[p + 1] - h->part_kx[p];
-      const char* sbuf = (const char*)h->snd[f] + (size_t)h->seg.base[p] * cb;
-      size_t scount = nyl * kxl_p * Kz * 2;
-      size_t rows_p = h->part_j[p + 1] - h->part_j[p];
-      char* rbuf = (char*)fields[f] + (size_t)h->part_j[p] * h->d.M * cb;
-      size_t rcount = rows_p * h->d.M * 2;
-      if (p == me) { CHAN_CUDA(h, cudaMemcpyAsync(rbuf, sbuf, scount * h->prec, cudaMemcpyDeviceToDevice, h->stream)); continue; }
-      CHAN_NCCL(h, ncclSend(sbuf, scount, real_type(h), p, comm, h->stream));
-      CHAN_NCCL(h, ncclRecv(rbuf, rcount, real_type(h), p, comm, h->stream));
-    }
-    CHAN_NCCL(h, ncclGroupEnd());
-  }
-  return CHAN_OK;
-}
+int exchange_to_pencils(chan_handle* h, int nf, void* const* fields) { return exchange(h, nf, fields, h->snd, false); }
 
 // velocity maxima of calcUmax: replaces the three MPI_Allreduce(MAX) of reduceMAX (hit_mpi.c:427-447).
 // The slots hold non-negative doubles as ordered bit patterns, so an unsigned max is a float max.

@@ -175,6 +175,7 @@ struct ElimVar {
 };
 
 template <typename T> __device__ __forceinline__ double rnd(double x) { return (double)(T)x; }
+template <typename T2> __device__ __forceinline__ T2 mk0() { T2 z; z.x = 0; z.y = 0; return z; }
 
 // ---- unfused building blocks (operator-level API, calcVdV) -------------------
 // out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
@@ -289,53 +290,72 @@ __global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
   const long st = 2 * a.M; const int ny = a.ny; const int c = md.c;
   const bool with_mean = md.zero_mode && a.use_mean;
   const Prefetch pf(ny);
-  // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w
+  // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w   (two rows of loads in flight)
   {
     ElimD1 eu, ew;
+    const bool omega = a.op == OP_OMEGA;
+    T2 z0 = omega ? mk0<T2>() : a.dv[md.m], z1 = omega ? mk0<T2>() : a.g[md.m];
+    T r0 = omega ? ((const T*)a.u)[md.e] : (T)0, r1 = omega ? ((const T*)a.w)[md.e] : (T)0;
     for (int j = 0; j < ny; j++) {
-      long cm = (long)j * a.M + md.m;
-      if (a.op != OP_OMEGA) { pf(a.dv + cm, a.M, j, 1); pf(a.g + cm, a.M, j, 1); }
+      long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
+      if (!omega) { pf(a.dv + cm, a.M, j, 1); pf(a.g + cm, a.M, j, 1); }
+      T2 z0n = z0, z1n = z1; T r0n = r0, r1n = r1;
+      if (j + 1 < ny) {
+        if (omega) { r0n = ((const T*)a.u)[re + st]; r1n = ((const T*)a.w)[re + st]; }
+        else { z0n = a.dv[cm + a.M]; z1n = a.g[cm + a.M]; }
+      }
       T u, w;
-      if (a.op == OP_OMEGA) { u = ((const T*)a.u)[(long)j * st + md.e]; w = ((const T*)a.w)[(long)j * st + md.e]; }
+      if (omega) { u = r0; w = r1; }
       else {
-        uw_comp<T, T2>(wv, md, md.zero_mode, a.dv[cm], a.g[cm], c, u, w);
+        uw_comp<T, T2>(wv, md, md.zero_mode, z0, z1, c, u, w);
         if (with_mean) u = c ? (T)0 : a.mean_u[j];                 // writeUmean (nonLinear.c:19-21)
       }
       eu.step(a.yt.d1[0], 0, j, ny, (double)u, a.sA, st, md.e);
       ew.step(a.yt.d1[0], 0, j, ny, (double)w, a.sB, st, md.e);
+      z0 = z0n; z1 = z1n; r0 = r0n; r1 = r1n;
     }
   }
   // pass 2 (down): back-substitute, build omega (calcOmegakernel, convolution_kernels.cu:46-53)
   {
     double xu = 0.0, xw = 0.0;
+    const bool omega = a.op == OP_OMEGA;
+    struct Row { double dA, dB; T2 v, a0, a1; };       // a0,a1 = (dv,g) or (u,w) of the row
+    Row r;
+    { long cm = (long)(ny - 1) * a.M + md.m, re = (long)(ny - 1) * st + md.e;
+      r.dA = a.sA[re]; r.dB = a.sB[re]; r.v = a.v[cm];
+      r.a0 = omega ? a.u[cm] : a.dv[cm]; r.a1 = omega ? a.w[cm] : a.g[cm]; }
     for (int j = ny - 1; j >= 0; j--) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
       pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.v + cm, a.M, j, -1);
-      if (a.op != OP_OMEGA) { pf(a.dv + cm, a.M, j, -1); pf(a.g + cm, a.M, j, -1); }
+      if (!omega) { pf(a.dv + cm, a.M, j, -1); pf(a.g + cm, a.M, j, -1); }
+      Row n = r;
+      if (j > 0) {
+        n.dA = a.sA[re - st]; n.dB = a.sB[re - st]; n.v = a.v[cm - a.M];
+        n.a0 = omega ? a.u[cm - a.M] : a.dv[cm - a.M]; n.a1 = omega ? a.w[cm - a.M] : a.g[cm - a.M];
+      }
       double cp = __ldg(a.yt.d1[0].cp + j);
-      xu = a.sA[re] - cp * xu; xw = a.sB[re] - cp * xw;
+      xu = r.dA - cp * xu; xw = r.dB - cp * xw;
       T dudy = (T)xu, dwdy = (T)xw;
       T u, w, up, wp;
-      if (a.op == OP_OMEGA) {
-        T2 uz = a.u[cm], wz = a.w[cm];
-        u = own<T2, T>(uz, c); up = other<T2, T>(uz, c); w = own<T2, T>(wz, c); wp = other<T2, T>(wz, c);
+      if (omega) {
+        u = own<T2, T>(r.a0, c); up = other<T2, T>(r.a0, c); w = own<T2, T>(r.a1, c); wp = other<T2, T>(r.a1, c);
       } else {
-        T2 dvz = a.dv[cm], gz = a.g[cm];
-        uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, c, u, w);
-        uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, c ^ 1, up, wp);
+        uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c, u, w);
+        uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c ^ 1, up, wp);
         if (with_mean) { u = c ? (T)0 : a.mean_u[j]; up = c ? a.mean_u[j] : (T)0; }
       }
-      T vp = other<T2, T>(a.v[cm], c);
+      T vp = other<T2, T>(r.v, c);
       T s = wv.sc;
       T o1 = dwdy - s * wv.k3 * vp;                    // omega_x = dw/dy - i k3 v
       T o2 = s * (wv.k3 * up - wv.k1 * wp);            // omega_y = i (k3 u - k1 w)
       T o3 = -dudy + s * wv.k1 * vp;                   // omega_z = -du/dy + i k1 v
-      if (a.op != OP_OMEGA) { ((T*)a.u)[re] = u; ((T*)a.w)[re] = w; }
+      if (!omega) { ((T*)a.u)[re] = u; ((T*)a.w)[re] = w; }
       ((T*)a.ox)[re] = o1; ((T*)a.oy)[re] = o2; ((T*)a.oz)[re] = o3;
       if (md.zero_mode && c == 0 && a.sc) {            // readUtau (convolution.c:14-16)
         if (j == 0) a.sc->dudy_wall[0] = (double)dudy;
         if (j == ny - 1) a.sc->dudy_wall[1] = (double)dudy;
       }
+      r = n;
     }
   }
 }
@@ -354,31 +374,42 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
   const T* phiR = (const T*)a.phi; const T* gR = (const T*)a.g;
   const T2* H1 = a.ox; const T2* H3 = a.oz; const T* H2R = (const T*)a.oy;
   const Prefetch pf(ny);
+  // Every pass keeps two rows in flight: the loads of the next row are issued before the current
+  // row is computed (the sweeps are latency-bound: one dependent row per thread otherwise).
   // P1 (up): eliminate d/dy of phi, g and hv = -i (k1 H1 + k3 H3)  (calcHvgkernel, nonLinear_kernels.cu:129-130)
   {
     ElimD1 ep, eg, eh;
+    T2 h1 = H1[md.m], h3 = H3[md.m]; T p = phiR[e], g = gR[e];
     for (int j = 0; j < ny; j++) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + e;
       pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
-      T h1p = other<T2, T>(H1[cm], c), h3p = other<T2, T>(H3[cm], c);
+      T2 h1n = h1, h3n = h3; T pn = p, gn = g;
+      if (j + 1 < ny) { h1n = H1[cm + a.M]; h3n = H3[cm + a.M]; pn = phiR[re + st]; gn = gR[re + st]; }
+      T h1p = other<T2, T>(h1, c), h3p = other<T2, T>(h3, c);
       T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
-      ep.step(a.yt.d1[0], 0, j, ny, (double)phiR[re], a.sA, st, e);
-      eg.step(a.yt.d1[0], 0, j, ny, (double)gR[re], a.sB, st, e);
+      ep.step(a.yt.d1[0], 0, j, ny, (double)p, a.sA, st, e);
+      eg.step(a.yt.d1[0], 0, j, ny, (double)g, a.sB, st, e);
       eh.step(a.yt.d1[0], 0, j, ny, (double)hv, a.sC, st, e);
+      h1 = h1n; h3 = h3n; p = pn; g = gn;
     }
   }
   // P2 (down): phi', g', hv' ; eliminate d/dy of phi', g' (second derivative = d/dy twice, Q4)
   {
     ElimD1 ep, eg;
     double xp = 0.0, xg = 0.0, xh = 0.0;
+    long re0 = (long)(ny - 1) * st + e;
+    double dA = a.sA[re0], dB = a.sB[re0], dC = a.sC[re0];
     for (int jj = 0; jj < ny; jj++) {
       int j = ny - 1 - jj; long re = (long)j * st + e;
       pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sC + re, st, j, -1);
+      double dAn = dA, dBn = dB, dCn = dC;
+      if (j > 0) { dAn = a.sA[re - st]; dBn = a.sB[re - st]; dCn = a.sC[re - st]; }
       double cp = __ldg(a.yt.d1[0].cp + j);
-      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg; xh = a.sC[re] - cp * xh;
+      xp = dA - cp * xp; xg = dB - cp * xg; xh = dC - cp * xh;
       a.sC[re] = rnd<T>(xh);
       ep.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xp), a.sA, st, e);
       eg.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xg), a.sB, st, e);
+      dA = dAn; dB = dBn; dC = dCn;
     }
   }
   // P3 (up): phi'', g'' -> explicit RK update (rk_step_1/2, RK3_kernels.cu:76-80,138-142) -> eliminate implicit solves
@@ -388,28 +419,36 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     ElimVar<2> ev;
     double* const ss[2] = { a.sA, a.sB };
     double xp = 0.0, xg = 0.0;
+    const T* RpR = (const T*)a.Rphi; const T* RgR = (const T*)a.Rg;
+    struct Row { double dA, dB, dC; T2 h1, h3; T h2, p, g, rp, rg; };
+    Row r;
+    r.dA = a.sA[e]; r.dB = a.sB[e]; r.dC = a.sC[e]; r.h1 = H1[md.m]; r.h3 = H3[md.m];
+    r.h2 = H2R[e]; r.p = phiR[e]; r.g = gR[e]; r.rp = RpR[e]; r.rg = RgR[e];
     for (int j = 0; j < ny; j++) {
       long cm = (long)j * a.M + md.m, re = (long)j * st + e;
       pf(a.sA + re, st, j, 1); pf(a.sB + re, st, j, 1); pf(a.sC + re, st, j, 1);
       pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(H2R + re, st, j, 1);
       pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
-      pf((const T*)a.Rphi + re, st, j, 1); pf((const T*)a.Rg + re, st, j, 1);
+      pf(RpR + re, st, j, 1); pf(RgR + re, st, j, 1);
+      Row n = r;
+      if (j + 1 < ny) {
+        n.dA = a.sA[re + st]; n.dB = a.sB[re + st]; n.dC = a.sC[re + st]; n.h1 = H1[cm + a.M]; n.h3 = H3[cm + a.M];
+        n.h2 = H2R[re + st]; n.p = phiR[re + st]; n.g = gR[re + st]; n.rp = RpR[re + st]; n.rg = RgR[re + st];
+      }
       double cp = __ldg(a.yt.d1[1].cp + (ny - 1 - j));
-      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
+      xp = r.dA - cp * xp; xg = r.dB - cp * xg;
       T pyy = (T)xp, gyy = (T)xg;
-      T2 h1 = H1[cm], h3 = H3[cm];
-      T h1p = other<T2, T>(h1, c), h3p = other<T2, T>(h3, c);
-      T rp_new = (T)a.sC[re] - wv.kk * H2R[re];                       // calcHvvkernel (:180-181)
+      T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
+      T rp_new = (T)r.dC - wv.kk * r.h2;                              // calcHvvkernel (:180-181)
       T rg_new = s * (wv.k3 * h1p - wv.k1 * h3p);                     // h_g = i (k3 H1 - k1 H3) (:132-133)
-      T p = phiR[re], g = gR[re];
-      T rp_old = ((const T*)a.Rphi)[re], rg_old = ((const T*)a.Rg)[re];
-      T pw = p + dt * (a.alpha * a.nuT * (pyy - wv.kk * p) + a.dseda * rp_old);
-      T gw = g + dt * (a.alpha * a.nuT * (gyy - wv.kk * g) + a.dseda * rg_old);
+      T pw = r.p + dt * (a.alpha * a.nuT * (pyy - wv.kk * r.p) + a.dseda * r.rp);
+      T gw = r.g + dt * (a.alpha * a.nuT * (gyy - wv.kk * r.g) + a.dseda * r.rg);
       pw = pw + dt * a.gammad * rp_new;
       gw = gw + dt * a.gammad * rg_new;
       ((T*)a.Rphi)[re] = rp_new; ((T*)a.Rg)[re] = rg_new;
       const double f[2] = { (double)pw, (double)gw };
       ev.step(a.yt.d2[0], 0, j, ny, f, true, wv.kkd, Dimp, ss, st, e, a.sP, a.M, md.m);
+      r = n;
     }
   }
   // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new
@@ -417,30 +456,39 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
     ElimVar<1> eh;
     double* const ss[1] = { a.sA };
     double xp = 0.0, xg = 0.0;
+    long re0 = (long)(ny - 1) * st + e;
+    double dA = a.sA[re0], dB = a.sB[re0], cp = a.sP[(long)(ny - 1) * a.M + md.m];
     for (int jj = 0; jj < ny; jj++) {
       int j = ny - 1 - jj; long re = (long)j * st + e;
       pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sP + (long)j * a.M + md.m, a.M, j, -1);
-      double cp = a.sP[(long)j * a.M + md.m];
-      xp = a.sA[re] - cp * xp; xg = a.sB[re] - cp * xg;
-      // both components of a mode share the pivot row: every lane must have read row j before
-      // any lane overwrites it with the Helmholtz pivot of the lagging row (next iteration)
+      double dAn = dA, dBn = dB, cpn = cp;
+      // rows below j are still the implicit-solve data: the Helmholtz elimination lags one row ABOVE
+      if (j > 0) { dAn = a.sA[re - st]; dBn = a.sB[re - st]; cpn = a.sP[(long)(j - 1) * a.M + md.m]; }
+      xp = dA - cp * xp; xg = dB - cp * xg;
+      // both components of a mode share the pivot row: every lane must have read its pivots before
+      // any lane overwrites row j+1 with the Helmholtz pivot of the lagging row
       __syncwarp();
       ((T*)a.g)[re] = (T)xg;
       ((T*)a.phi)[re] = (T)xp;
       const double f[1] = { rnd<T>(xp) };
       eh.step(a.yt.d2[1], 1, jj, ny, f, false, wv.kkd, 0.0, ss, st, e, a.sP, a.M, md.m);
+      dA = dAn; dB = dBn; cp = cpn;
     }
   }
   // P5 (up): v ; eliminate d/dy v
   {
     ElimD1 ev;
     double xv = 0.0;
+    double dA = a.sA[e], cp = a.sP[md.m];
     for (int j = 0; j < ny; j++) {
       long re = (long)j * st + e;
       pf(a.sA + re, st, j, 1); pf(a.sP + (long)j * a.M + md.m, a.M, j, 1);
-      xv = a.sA[re] - a.sP[(long)j * a.M + md.m] * xv;
+      double dAn = dA, cpn = cp;
+      if (j + 1 < ny) { dAn = a.sA[re + st]; cpn = a.sP[(long)(j + 1) * a.M + md.m]; }
+      xv = dA - cp * xv;
       ((T*)a.v)[re] = (T)xv;
       ev.step(a.yt.d1[0], 0, j, ny, rnd<T>(xv), a.sA, st, e);
+      dA = dAn; cp = cpn;
     }
   }
   // P6 (down): dv

@@ -154,6 +154,14 @@ int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_pencils);
 /* splits n items over `size` ranks as evenly as possible: [*start, *start+*count) */
 int chan_partition(int n, int size, int rank, int* start, int* count);
 int chan_active_kx(int nx);     /* 2*floor(nx/3)+1 */
+/* What rank `rank` of `size` exchanges with `peer` for ONE field in the pencil -> plane direction
+ * (the transposeYZX2XYZ of channel_cuda_mpi.c:95-128), in complex elements:
+ *   out[0], out[1]  offset / count inside the rank's pencil-side field  F[NY][Kx_local][Kz]  (sent)
+ *   out[2], out[3]  offset / count inside its plane-side buffer (per-source blocks)        (received)
+ *   out[4], out[5]  first active-kx index and count of the peer's slab
+ *   out[6], out[7]  first y plane and count of the peer's slab
+ * The plane -> pencil direction swaps the roles of [0,1] and [2,3].  Pure host arithmetic. */
+int chan_exchange_layout(int nx, int ny, int nz, int size, int rank, int peer, long* out8);
 int chan_active_kz(int nz);     /* floor((2nz-2)/3)+1 */
 
 #ifdef __cplusplus
