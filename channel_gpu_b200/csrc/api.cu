@@ -73,7 +73,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
       { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 256 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 } };
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 } };
     for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
   }
   Dims& d = h->d;
@@ -133,6 +133,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   h->io_bytes = ref_bytes(h);
   if ((rc = alloc_dev(h, &h->io_buf, h->io_bytes))) return rc;
   if ((rc = build_tables(h))) return rc;
+  // wall-normal stage: bit 0 = segment-parallel pre kernel, bit 1 = segment-parallel post kernel.
+  // Measured on B200 (profiles/): the register version of `pre` always wins; `post` is instruction-
+  // and latency-bound in both forms and the register version only pays when there are too few chains
+  // to fill the GPU with one thread per chain (small grids, many GPUs).
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = 1 | ((2 * d.M < 148L * 256) ? 2 : 0);
+  if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
 }
@@ -141,7 +147,7 @@ extern "C" void chan_destroy(chan_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
-                   h->Q, h->ytab_store, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
+                   h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
                    h->snd[0], h->snd[1], h->snd[2] };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
@@ -275,13 +281,13 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if (!h || n < 0 || n > 2) return CHAN_ERR_ARG;
   int rc, t;
   t = t_begin(h, CHAN_STAGE_PRE);
-  if ((rc = launch_pencil_pre(h))) return rc;            // calcUW + writeUmean + d/dy + calcOmega
+  if ((rc = (h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
   t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
   t_end(h, t); t = t_begin(h, CHAN_STAGE_SCALAR);
   if ((rc = launch_scalar_stage(h, n))) return rc;        // mean flow, calcDt
   t_end(h, t); t = t_begin(h, CHAN_STAGE_POST);
-  rc = launch_pencil_post(h, n);                          // RK explicit + h_v,h_g + implicit + bi-Laplacian
+  rc = (h->tune.pencil_seg & 2) ? launch_pencil_post_seg(h, n) : launch_pencil_post(h, n);   // RK explicit + h_v,h_g + implicit + bi-Laplacian
   t_end(h, t);
   return rc;
 }

@@ -96,6 +96,9 @@ struct chan_handle {
   void* Q; int plane_batch;
   // tables
   double* ytab_store; chan::YTabs yt;
+  // segment-parallel y stage (kernels_pencil_seg.cu): segment length, prefix-product tables of the
+  // folded d/dy LU for that length, per-mode pivots of the Helmholtz / implicit matrices [NY][M]
+  int seg_S; double *seg_pf, *seg_pb; double *pivH, *pivI; int pivH_ready;
   void *tw_x, *tw_z; chan::FftPlan px, pz;
   int *invx, *invz, *posx, *posz;   // digit-reversal tables of the two plans
   void *mean_a, *mean_b;        // host-mesh differences in T (meanUevol.c:230-231)
@@ -108,7 +111,7 @@ struct chan_handle {
   chan::SegMap seg;               // plane-side segmentation (identical for every field)
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
@@ -130,6 +133,11 @@ int perm_pos_of(const FftPlan& p, int n);
 int launch_pencil_pre(chan_handle* h);
 int launch_pencil_post(chan_handle* h, int n);
 int launch_op(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt);
+// kernels_pencil_seg.cu
+int seg_supported(chan_handle* h);
+int seg_setup(chan_handle* h);
+int launch_pencil_pre_seg(chan_handle* h);
+int launch_pencil_post_seg(chan_handle* h, int n);
 // kernels_plane.cu
 int launch_nonlinear_planes(chan_handle* h);                 // u,v,w,omega -> H (in ox,oy,oz)
 int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields

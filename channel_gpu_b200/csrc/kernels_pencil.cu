@@ -30,58 +30,9 @@
 //                  here: truncated modes are not stored)
 // The state type T rounds exactly where the reference's cast_kernel does (after
 // every solve) and where its pointwise kernels compute in float.
-#include "chan_internal.h"
+#include "pencil_common.cuh"
 
 namespace chan {
-
-template <typename T>
-struct PArgs {
-  typedef typename Vec2<T>::type T2;
-  T2 *phi, *g, *v, *dv, *Rphi, *Rg, *u, *w, *ox, *oy, *oz;
-  double *sA, *sB, *sC, *sP;
-  const T* mean_u;
-  Scalars* sc;
-  YTabs yt;
-  int ny, Kz, ikx0, kxmax, Kx;
-  long M;
-  T k1fac, k3fac;          // PI2/LX, PI2/LZ in the state type (RK3_kernels.cu:53-54)
-  T nuT;                   // 1.0f/REYNOLDS in the state type (RK3_kernels.cu:58)
-  double nuD;              // 1.0/REYNOLDS in double (implicitStep_nu_double.cu:133)
-  double reD;              // (double)REYNOLDS (bilplacSolver_double.cu:58)
-  int n;                   // RK substep
-  T alpha, dseda, gammad, betha;
-  // generic operator launches
-  int op; T2 *f0, *f1, *f2; T op_betha, op_dt; int use_mean;
-};
-
-struct Mode {
-  long m; int c; long e;   // mode, component, real chain index
-  int kxi, kzi; bool zero_mode;
-};
-
-template <typename T>
-struct Wave { T k1, k3, kk; double kkd; T sc; T sp; };   // sc = sign of own component of i*z: -1 (re), +1 (im)
-
-template <typename T>
-__device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) {
-  long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= 2 * a.M) return false;
-  md.e = e; md.m = e >> 1; md.c = (int)(e & 1);
-  int ikx = a.ikx0 + (int)(md.m / a.Kz);
-  md.kzi = (int)(md.m % a.Kz);
-  md.kxi = ikx <= a.kxmax ? ikx : ikx - a.Kx;
-  md.zero_mode = (md.kxi == 0 && md.kzi == 0);
-  wv.k1 = a.k1fac * (T)md.kxi;
-  wv.k3 = a.k3fac * (T)md.kzi;
-  wv.kk = wv.k1 * wv.k1 + wv.k3 * wv.k3;
-  double k1d = (double)a.k1fac * (double)md.kxi, k3d = (double)a.k3fac * (double)md.kzi;
-  wv.kkd = k1d * k1d + k3d * k3d;
-  wv.sc = md.c ? (T)1 : (T)-1;
-  wv.sp = -wv.sc;
-  return true;
-}
-
-__device__ __forceinline__ int phys_row(int dir, int jj, int ny) { return dir ? ny - 1 - jj : jj; }
 
 // The sweeps are latency-bound (one dependent row per thread in flight): pull the rows a few steps
 // ahead into L2, one request per 128-byte line (lanes 0 and 16 of the warp's 256-byte row segment).
@@ -97,10 +48,6 @@ struct Prefetch {
   }
 };
 
-template <typename T2, typename T>
-__device__ __forceinline__ T own(const T2& z, int c) { return c ? z.y : z.x; }
-template <typename T2, typename T>
-__device__ __forceinline__ T other(const T2& z, int c) { return c ? z.x : z.y; }
 
 // ---- fixed-matrix compact d/dy: elimination with the folded LU ---------------
 struct ElimD1 {
@@ -174,9 +121,6 @@ struct ElimVar {
   }
 };
 
-template <typename T> __device__ __forceinline__ double rnd(double x) { return (double)(T)x; }
-template <typename T2> __device__ __forceinline__ T2 mk0() { T2 z; z.x = 0; z.y = 0; return z; }
-
 // ---- unfused building blocks (operator-level API, calcVdV) -------------------
 // out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
 template <typename T>
@@ -209,46 +153,16 @@ __device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, 
   }
 }
 
-// ---- wall correction of the bi-Laplacian (setBoundaryCond, bilplacSolver_double.cu:6-296)
-struct BcFun { double v1, v2, dv1, dv2, ddv1, ddv2; };
-// the six functions exactly as written at :174-217: half of the exponentials are fp32 `expf`,
-// and the l2 lines take exp(-l1*(1+y)) in their first bracket — mirrored, it
-// defines the reference's v.
-__device__ __forceinline__ BcFun bc_functions(double l1, double l2, double D, double y) {
-  double E1m = (double)expf((float)(-l1 * (1.0 - y)));
-  double E1p = exp(-l1 * (1.0 + y));
-  double E2m = (double)expf((float)(-l2 * (1.0 - y)));
-  double E2p = exp(-l2 * (1.0 + y));
-  double p1 = 1.0 + exp(-l1 * 2.0), m1 = 1.0 - exp(-l1 * 2.0);
-  double p2 = 1.0 + exp(-l2 * 2.0), m2 = 1.0 - exp(-l2 * 2.0);
-  BcFun r;
-  r.v1 = 0.5 * D * ((E1m + E1p) / p1 - (E1m - E1p) / m1);
-  r.v1 += 0.5 * D * (-(E2m + E1p) / p2 + (E2m - E2p) / m2);
-  r.v2 = 0.5 * D * ((E1m + E1p) / p1 + (E1m - E1p) / m1);
-  r.v2 += 0.5 * D * (-(E2m + E1p) / p2 - (E2m - E2p) / m2);
-  r.dv1 = 0.5 * D * l1 * ((E1m - E1p) / p1 - (E1m + E1p) / m1);
-  r.dv1 += 0.5 * D * l2 * (-(E2m - E1p) / p2 + (E2m + E2p) / m2);
-  r.dv2 = 0.5 * D * l1 * ((E1m - E1p) / p1 + (E1m + E1p) / m1);
-  r.dv2 += 0.5 * D * l2 * (-(E2m - E1p) / p2 - (E2m + E2p) / m2);
-  r.ddv1 = 0.5 * ((E1m + E1p) / p1 - (E1m - E1p) / m1);
-  r.ddv2 = 0.5 * ((E1m + E1p) / p1 + (E1m - E1p) / m1);
-  return r;
-}
-
 // phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
 template <typename T>
 __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
                            T* phi, T* v, T* dv, double dvm, double dvp) {
   const long st = 2 * a.M; const int ny = a.ny;
   if (!((double)dt > 1e-8)) return;                       // bilplacSolver_double.cu:314 (Q6)
-  if (md.zero_mode) {                                     // :252-262
-    for (int j = 0; j < ny; j++) { long i = (long)j * st + md.e; phi[i] = 0; v[i] = 0; dv[i] = 0; }
-    return;
-  }
-  double l1 = sqrt(wv.kkd + a.reD / ((double)dt * (double)betha));
-  double l2 = sqrt(wv.kkd);
-  double D = 1.0 / (l1 * l1 - l2 * l2);
-  BcFun p = bc_functions(l1, l2, D, 1.0), q = bc_functions(l1, l2, D, -1.0);
+  // mode (0,0) is zeroed (:252-262); it runs the same instructions on a dummy kk so that the
+  // shuffles inside bc_functions stay warp-uniform
+  const BcCoef k = bc_coef(md.zero_mode ? 1.0 : wv.kkd, a.reD, (double)dt, (double)betha);
+  BcFun p = bc_functions(k, 1.0, md.c), q = bc_functions(k, -1.0, md.c);
   double det = q.dv1 * p.dv2 - p.dv1 * q.dv2;
   double c1 = p.dv2 * dvm - q.dv2 * dvp; c1 = -c1 / det;
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
@@ -256,27 +170,14 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   for (int j = 0; j < ny; j++) {
     long i = (long)j * st + md.e;
     pf(phi + i, st, j, 1); pf(v + i, st, j, 1); pf(dv + i, st, j, 1);
-    BcFun f = bc_functions(l1, l2, D, __ldg(a.yt.y + j));
+    BcFun f = bc_functions(k, __ldg(a.yt.y + j), md.c);
     double pp = (double)phi[i], vv = (double)v[i], dd = (double)dv[i];
     pp = pp + c1 * f.ddv1 + c2 * f.ddv2;
     dd = dd + c1 * f.dv1 + c2 * f.dv2;
     vv = vv + c1 * f.v1 + c2 * f.v2;
+    if (md.zero_mode) { pp = 0.0; vv = 0.0; dd = 0.0; }
     phi[i] = (T)pp; v[i] = (T)vv; dv[i] = (T)dd;
   }
-}
-
-// ---- pointwise pieces ----------------------------------------------------------
-// own component of u, w from complex dv, g (calcUWkernel, nonLinear_kernels.cu:53-82)
-template <typename T, typename T2>
-__device__ __forceinline__ void uw_comp(const Wave<T>& wv, const Mode& md, bool zero_mode, const T2& dvz, const T2& gz, int c,
-                                        T& u, T& w) {
-  T kk = zero_mode ? (T)1 : wv.kk;
-  T s = c ? (T)1 : (T)-1;
-  T dp = other<T2, T>(dvz, c), gp = other<T2, T>(gz, c);
-  // u = i (k1 dv - k3 g)/kk ; w = i (k3 dv + k1 g)/kk, written in the reference's operation order
-  u = s * (wv.k1 * dp - wv.k3 * gp) / kk;
-  w = s * (wv.k3 * dp + wv.k1 * gp) / kk;
-  if (zero_mode) { u = 0; w = 0; }
 }
 
 // =================================================================================
@@ -567,7 +468,7 @@ __global__ void __launch_bounds__(128) op_kernel(PArgs<T> a) {
 
 // ---------------------------------------------------------------------------------
 template <typename T>
-static void fill_args(chan_handle* h, PArgs<T>& a) {
+void fill_pencil_args(chan_handle* h, PArgs<T>& a) {
   typedef typename Vec2<T>::type T2;
   a.phi = (T2*)h->phi; a.g = (T2*)h->g; a.v = (T2*)h->v; a.dv = (T2*)h->dv; a.Rphi = (T2*)h->Rphi; a.Rg = (T2*)h->Rg;
   a.u = (T2*)h->u; a.w = (T2*)h->w; a.ox = (T2*)h->ox; a.oy = (T2*)h->oy; a.oz = (T2*)h->oz;
@@ -592,7 +493,7 @@ static const float kBetha[3] = { 37.0f / 160.0f, 5.0f / 24.0f, 1.0f / 6.0f };   
 
 template <typename T>
 static int pre_t(chan_handle* h) {
-  PArgs<T> a; fill_args<T>(h, a);
+  PArgs<T> a; fill_pencil_args<T>(h, a);
   long nchain = 2 * h->d.M;
   pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
   h->launches++;
@@ -601,7 +502,7 @@ static int pre_t(chan_handle* h) {
 }
 template <typename T>
 static int post_t(chan_handle* h, int n) {
-  PArgs<T> a; fill_args<T>(h, a);
+  PArgs<T> a; fill_pencil_args<T>(h, a);
   a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
   long nchain = 2 * h->d.M;
   pencil_post_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
@@ -612,7 +513,7 @@ static int post_t(chan_handle* h, int n) {
 template <typename T>
 static int op_t(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt) {
   typedef typename Vec2<T>::type T2;
-  PArgs<T> a; fill_args<T>(h, a);
+  PArgs<T> a; fill_pencil_args<T>(h, a);
   a.op = op; a.f0 = (T2*)f0; a.f1 = (T2*)f1; a.f2 = (T2*)f2; a.op_betha = (T)betha; a.op_dt = (T)dt;
   long nchain = 2 * h->d.M;
   unsigned grid = (unsigned)((nchain + 127) / 128);
@@ -622,6 +523,9 @@ static int op_t(chan_handle* h, int op, void* f0, void* f1, void* f2, double bet
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
 }
+
+template void fill_pencil_args<float>(chan_handle*, PArgs<float>&);
+template void fill_pencil_args<double>(chan_handle*, PArgs<double>&);
 
 int launch_pencil_pre(chan_handle* h) { return h->prec == 4 ? pre_t<float>(h) : pre_t<double>(h); }
 int launch_pencil_post(chan_handle* h, int n) { return h->prec == 4 ? post_t<float>(h, n) : post_t<double>(h, n); }
