@@ -276,21 +276,27 @@ def main():
            "note": "set_fields (pinned H2D + relayout) + rk_init + K x (rk_step + D2H scalars) + get_fields (relayout + D2H); field copies amortised over K steps"}
 
     # ---- roofline of the dominant kernel ---------------------------------------------------
+    # algorithmic bytes per launch (P = one compact field, Qc = one x-padded field):
     peak, peak_src = measured_peaks()
-    P = sz["P"]; Qc = sz["Qc"]
-    stage_bytes = {"pencil_pre": 9 * P, "planes": 6 * P + 6 * Qc + 6 * Qc + 3 * Qc + 3 * Qc + 3 * P, "pencil_post": 13 * P}
-    stage_ms = {"pencil_pre": ms[0] / max(cnt[0], 1), "planes": ms[1] / max(cnt[1], 1), "scalar": ms[2] / max(cnt[2], 1), "pencil_post": ms[3] / max(cnt[3], 1)}
-    stages = {k: {"ms": stage_ms[k], "alg_GB": stage_bytes[k] / 1e9, "GBps": stage_bytes[k] / 1e6 / stage_ms[k]} for k in stage_bytes}
-    stages["scalar"] = {"ms": stage_ms["scalar"]}
-    dom = max(stage_bytes, key=lambda k: stage_ms[k])
+    P = sz["P"] / world; Qc = sz["Qc"] / world
+    kern = {"pencil_pre": (0, 9 * P), "pencil_post": (3, 13 * P), "xfft_inv": (5, 6 * P + 6 * Qc),
+            "zstage": (6, 9 * Qc), "xfft_fwd": (7, 3 * Qc + 3 * P)}
+    stages = {}
+    for name, (sid, nbytes) in kern.items():
+        t = ms[sid] / max(cnt[sid], 1)
+        stages[name] = {"ms": t, "launches": cnt[sid], "alg_GB": nbytes / 1e9, "GBps": nbytes / 1e6 / t if t > 0 else None}
+    stages["scalar"] = {"ms": ms[2] / max(cnt[2], 1)}
+    stages["plane_stage_total"] = {"ms": ms[1] / max(cnt[1], 1)}
+    dom = max(kern, key=lambda k: stages[k]["ms"] * stages[k]["launches"])
     traffic = None
     pj = os.path.join(ROOT, "profiles", "ncu_summary.json")
     if os.path.exists(pj):
         traffic = json.load(open(pj)).get(dom, {}).get("dram_bytes_per_launch")
-    ach = stage_bytes[dom] / 1e6 / stage_ms[dom]
+    ach = stages[dom]["GBps"]
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
-                "peak_source": peak_src, "alg_bytes_per_launch": stage_bytes[dom],
-                "step_frac": (3 * (31 * P + 18 * Qc) / 1e6 / step_ms) / peak}
+                "peak_source": peak_src, "alg_bytes_per_launch": kern[dom][1],
+                "note": "algorithmic bytes / CUDA-event time of the kernel inside the timed steps; traffic = dram bytes of one ncu --set full capture (profiles/ncu_summary.json)",
+                "step_frac": (3 * (31 * sz["P"] + 18 * sz["Qc"]) / world / 1e6 / step_ms) / peak}
 
     out = {"metric": "RK3 steps/s", "value": value, "unit": "steps/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms,
            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if prec == 8 else "f32",

@@ -137,7 +137,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // Measured on B200 (profiles/): the register version of `pre` always wins; `post` is instruction-
   // and latency-bound in both forms and the register version only pays when there are too few chains
   // to fill the GPU with one thread per chain (small grids, many GPUs).
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = 1 | ((2 * d.M < 148L * 256) ? 2 : 0);
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = 1 | ((2 * d.M < 148L * 64) ? 2 : 0);
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
@@ -254,7 +254,8 @@ extern "C" int chan_rk_init(chan_handle* h) {
 }
 
 // ---- optional stage timing ----------------------------------------------------------
-static int t_begin(chan_handle* h, int stage) {
+namespace chan {
+int timing_begin(chan_handle* h, int stage) {
   if (!h->timing || h->n_ev >= 1024) return -1;
   int i = h->n_ev++;
   if (!h->ev0[i]) { cudaEventCreate(&h->ev0[i]); cudaEventCreate(&h->ev1[i]); }
@@ -262,7 +263,10 @@ static int t_begin(chan_handle* h, int stage) {
   cudaEventRecord(h->ev0[i], h->stream);
   return i;
 }
-static void t_end(chan_handle* h, int i) { if (i >= 0) cudaEventRecord(h->ev1[i], h->stream); }
+void timing_end(chan_handle* h, int i) { if (i >= 0) cudaEventRecord(h->ev1[i], h->stream); }
+}  // namespace chan
+#define t_begin timing_begin
+#define t_end timing_end
 
 extern "C" int chan_set_timing(chan_handle* h, int on) { if (!h) return CHAN_ERR_ARG; h->timing = on; return CHAN_OK; }
 extern "C" int chan_get_stage_ms(chan_handle* h, double* ms, long* cnt) {

@@ -122,6 +122,8 @@ struct chan_handle {
 namespace chan {
 enum { OP_DERIV_Y = 1, OP_DERIV_YY, OP_HELM, OP_IMPLICIT, OP_BILAP, OP_VDV, OP_UW, OP_HVG, OP_OMEGA };
 int set_err(chan_handle* h, int code, const char* fmt, ...);
+int timing_begin(chan_handle* h, int stage);     // api.cu: CUDA-event pair around a stage (no-op unless chan_set_timing)
+void timing_end(chan_handle* h, int id);
 #define CHAN_CUDA(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
   return chan::set_err(h, CHAN_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 

@@ -24,8 +24,9 @@ static int exchange(chan_handle* h, int nf, void* const* pencil, void* const* pl
   ncclComm_t comm = (ncclComm_t)h->nccl_comm;
   const int S = h->cfg.size, me = h->cfg.rank;
   const size_t cb = 2 * (size_t)h->prec;
+  // one group for all fields: NCCL fuses the nf*(S-1) send/recv pairs into a single launch
+  CHAN_NCCL(h, ncclGroupStart());
   for (int f = 0; f < nf; f++) {
-    CHAN_NCCL(h, ncclGroupStart());
     for (int p = 0; p < S; p++) {
       long L[8];
       chan_exchange_layout(h->d.nx, h->d.ny, h->d.nz, S, me, p, L);   // the layout the CPU tests check
@@ -36,8 +37,8 @@ static int exchange(chan_handle* h, int nf, void* const* pencil, void* const* pl
       CHAN_NCCL(h, ncclSend(sbuf, scount, real_type(h), p, comm, h->stream));
       CHAN_NCCL(h, ncclRecv(rbuf, rcount, real_type(h), p, comm, h->stream));
     }
-    CHAN_NCCL(h, ncclGroupEnd());
   }
+  CHAN_NCCL(h, ncclGroupEnd());
   return CHAN_OK;
 }
 // pencil fields -> h->rcv[f]: peer p receives my rows [j0_p, j0_p + nyl_p) of every field

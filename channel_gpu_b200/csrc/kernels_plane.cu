@@ -226,9 +226,13 @@ static int nonlinear_t(chan_handle* h) {
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = xf.j_start = z.j_start = js; xi.pb = xf.pb = z.pb = pb;
+    int t = timing_begin(h, CHAN_STAGE_XINV);
     int rc = launch_x_any<T>(h, true, xi, 6, pb); if (rc) return rc;
+    timing_end(h, t); t = timing_begin(h, CHAN_STAGE_Z);
     rc = launch_z<T, ZM_ROTOR>(h, z, 6, pb); if (rc) return rc;
+    timing_end(h, t); t = timing_begin(h, CHAN_STAGE_XFWD);
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
+    timing_end(h, t);
   }
   if (multi) { int rc = allreduce_umax(h); if (rc) return rc; rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
   return CHAN_OK;

@@ -34,8 +34,11 @@ def main():
         s0, c0 = cg.partition(Kx, size, rank)
         ikx = np.arange(s0, s0 + c0); kx = np.where(ikx <= g.nx // 3, ikx, ikx - Kx); ii = np.where(kx >= 0, kx, kx + g.nx)
         for name in ("ddv", "g", "v", "dv", "R_ddv", "R_g"):
-            got = ch.get_field(name)[ii]; want = g.full(f"{sub}/{name}")[ii]
-            e = rel(got, want); worst = max(worst, e / tol)
+            full = g.full(f"{sub}/{name}")
+            got = ch.get_field(name)[ii]; want = full[ii]
+            # slab error against the norm of the WHOLE field: a slab of high wavenumbers alone carries
+            # little energy, and fp32 round-off of the nonlinear term would dominate a per-slab ratio
+            e = float(np.linalg.norm((got - want).ravel()) / np.linalg.norm(full.ravel())); worst = max(worst, e / tol)
             if e >= tol:
                 print(f"[rank {rank}] {case} {name}: {e:.2e} >= {tol}", flush=True); sys.exit(1)
         sc = ch.scalars()
