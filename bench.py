@@ -225,6 +225,8 @@ def main():
     out_ddv_t = torch.empty_like(ddv_t).pin_memory(); out_g_t = torch.empty_like(g_t).pin_memory()
 
     ch = cg.Channel(nx, ny, nz, precision=prec, device=local, plane_batch=args.plane_batch, rank=rank, size=world, nccl_comm=comm)
+    if world > 1 and os.environ.get("CHAN_PEER", "1") != "0":
+        ch.enable_peer_exchange()
     ch.set_fields(ddv_p, g_p); ch.set_umean(um)
     ch.rk_init()
     ch.rk_step(W); ch.sync()
@@ -313,7 +315,7 @@ def main():
         out["e2e"]["value"] = K / float(t[0])
         S = world
         out["nvlink"] = {"bytes_per_gpu_per_step_each_way": int(3 * 9 * (P / S) * (S - 1) / S),
-                         "note": "9 field exchanges per substep, active modes only, NCCL grouped send/recv on the compute stream (not yet overlapped)"}
+                         "exchange": "NCCL grouped send/recv" if os.environ.get("CHAN_PEER", "1") == "0" else "peer stores over NVLink from pencil_pre / xfft_fwd (CUDA IPC) + 2 stream-ordered barriers per substep"}
     if rank == 0:
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_baseline_sample(cfg, prec)

@@ -65,6 +65,7 @@ def load_library():
         "chan_calc_hvg": [vp, vp, vp, vp], "chan_impose_symmetry": [vp, vp, vp],
         "chan_fft_backward_transpose": [vp, vp, vp],
         "chan_deriv_y_pencils_static": [vp, vp, C.c_long],
+        "chan_ipc_export": [vp, vp], "chan_ipc_import": [vp, ci, vp],
         "chan_partition": [ci, ci, ci, C.POINTER(ci), C.POINTER(ci)],
         "chan_active_kx": [ci], "chan_active_kz": [ci],
         "chan_exchange_layout": [ci, ci, ci, ci, ci, ci, C.POINTER(C.c_long)],
@@ -213,6 +214,18 @@ class Channel:
         self.rk_step(nsteps)
         self.sync()
         return self.get_fields()
+
+    def enable_peer_exchange(self):
+        """Multi-GPU: map every other rank's exchange buffers (CUDA IPC) so that the substep stores exchanged
+        fields straight into them over NVLink from the producing kernels.  torch.distributed carries the handles."""
+        import torch.distributed as dist
+        mine = C.create_string_buffer(9 * 64)
+        self._ck(self.L.chan_ipc_export(self.h, mine), "chan_ipc_export")
+        allh = [None] * self.size
+        dist.all_gather_object(allh, bytes(mine.raw))
+        for r, b in enumerate(allh):
+            self._ck(self.L.chan_ipc_import(self.h, r, b), "chan_ipc_import")
+        dist.barrier()
 
     def sync(self):
         self._ck(self.L.chan_sync(self.h), "chan_sync")

@@ -123,6 +123,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     const size_t pb_bytes = (size_t)d.nyl * d.Kx * d.Kz * csize(h);
     for (int f = 0; f < 6; f++) if ((rc = alloc_dev(h, &h->rcv[f], pb_bytes))) return rc;
     for (int f = 0; f < 3; f++) if ((rc = alloc_dev(h, &h->snd[f], pb_bytes))) return rc;
+    if ((rc = alloc_dev(h, (void**)&h->barrier_word, 256))) return rc;
   }
   const size_t rb = (size_t)d.ny * h->prec;
   if ((rc = alloc_dev(h, &h->mean_u, rb))) return rc;
@@ -146,14 +147,50 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
 extern "C" void chan_destroy(chan_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
+  for (int r = 0; r < 8; r++) if (r != h->cfg.rank) {
+    for (int f = 0; f < 6; f++) if (h->peer_rcv[r][f]) cudaIpcCloseMemHandle(h->peer_rcv[r][f]);
+    for (int f = 0; f < 3; f++) if (h->peer_H[r][f]) cudaIpcCloseMemHandle(h->peer_H[r][f]);
+  }
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
                    h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
-                   h->snd[0], h->snd[1], h->snd[2] };
+                   h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
+}
+
+// ---- peer-store exchange set-up ---------------------------------------------------------------------
+extern "C" int chan_ipc_export(chan_handle* h, void* out) {
+  if (!h || !out) return CHAN_ERR_ARG;
+  if (h->cfg.size < 2) return set_err(h, CHAN_ERR_STATE, "chan_ipc_export needs a multi-GPU handle");
+  void* bufs[9] = { h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5], h->ox, h->oy, h->oz };
+  for (int i = 0; i < 9; i++) {
+    cudaIpcMemHandle_t mh;
+    CHAN_CUDA(h, cudaIpcGetMemHandle(&mh, bufs[i]));
+    static_assert(sizeof(mh) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy((char*)out + 64 * i, &mh, 64);
+  }
+  return CHAN_OK;
+}
+extern "C" int chan_ipc_import(chan_handle* h, int peer, const void* in) {
+  if (!h || !in || peer < 0 || peer >= h->cfg.size) return CHAN_ERR_ARG;
+  if (peer == h->cfg.rank) return CHAN_OK;
+  for (int i = 0; i < 9; i++) {
+    cudaIpcMemHandle_t mh; memcpy(&mh, (const char*)in + 64 * i, 64);
+    void* p = 0;
+    CHAN_CUDA(h, cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess));
+    if (i < 6) h->peer_rcv[peer][i] = p; else h->peer_H[peer][i - 6] = p;
+  }
+  int have = 0;
+  for (int r = 0; r < h->cfg.size; r++) have += (r == h->cfg.rank || h->peer_rcv[r][0]) ? 1 : 0;
+  if (have == h->cfg.size) {
+    for (int f = 0; f < 6; f++) h->peer_rcv[h->cfg.rank][f] = h->rcv[f];
+    h->peer_H[h->cfg.rank][0] = h->ox; h->peer_H[h->cfg.rank][1] = h->oy; h->peer_H[h->cfg.rank][2] = h->oz;
+    h->peer_ready = (h->tune.pencil_seg & 1) ? 1 : 0;      // the register `pre` kernel is the producer
+  }
+  return CHAN_OK;
 }
 
 extern "C" const char* chan_last_error(const chan_handle* h) { return h ? h->err : "null handle"; }

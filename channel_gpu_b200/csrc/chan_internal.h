@@ -58,6 +58,10 @@ struct FftPlan {
 //   base[s] + (jl*width[s] + ikx - start[s])*Kz + kz      (in complex elements)
 struct SegMap { int nseg; int start[9]; int width[8]; long base[8]; };
 
+// Peer-store exchange (multi-GPU): where the wall-normal `pre` kernel delivers row j of plane-stage
+// input field f — straight into the receive buffer of the rank that owns plane j, over NVLink.
+struct PeerOut { void* rcv[8][6]; int part_j[9]; int nranks; long src_off[8]; };   // src_off[p] = nyl_p*ikx0*Kz (complex elements)
+
 // ---- handle ---------------------------------------------------------------
 struct Dims {
   int nx, ny, nz, nzp;          // NZ = complex z count, nzp = 2NZ-2 physical z points
@@ -107,6 +111,8 @@ struct chan_handle {
   // multi-GPU exchange (comm.cu): NCCL communicator owned by the caller, receive buffers of the 6
   // fields entering the plane stage, send buffers of the 3 leaving it, slab boundaries of all ranks
   void* nccl_comm; void* rcv[6]; void* snd[3];
+  // peer-store exchange: CUDA-IPC-mapped buffers of the other ranks (rcv[6] and the pencil fields H1..3)
+  int peer_ready; void* peer_rcv[8][6]; void* peer_H[8][3]; int* barrier_word;
   int part_kx[9], part_j[9];      // part_kx[r] = first active-kx index of rank r (part_kx[size] = Kx), same for planes
   chan::SegMap seg;               // plane-side segmentation (identical for every field)
   // boundary staging (reference layout <-> compact)
@@ -153,6 +159,7 @@ int launch_end_step(chan_handle* h);
 int exchange_to_planes(chan_handle* h, int nf, void* const* pencil_fields);      // -> h->rcv[0..nf)
 int exchange_to_pencils(chan_handle* h, int nf, void* const* pencil_fields);     // h->snd[0..nf) ->
 int allreduce_umax(chan_handle* h);
+int stream_barrier(chan_handle* h);                 // all ranks' work issued so far has completed
 int allreduce_sum_host(chan_handle* h, double* dev_buf, int n);
 int launch_stats(chan_handle* h, double* out4ny_dev);
 }  // namespace chan

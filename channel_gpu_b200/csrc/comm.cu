@@ -53,6 +53,14 @@ int allreduce_umax(chan_handle* h) {
   return CHAN_OK;
 }
 
+// Stream-ordered barrier across the ranks: a one-word all-reduce.  It completes on a rank only after
+// every rank has reached it in its own stream, i.e. after everything issued before it there (the
+// kernels that store into this rank's buffers over NVLink) has finished.
+int stream_barrier(chan_handle* h) {
+  CHAN_NCCL(h, ncclAllReduce(h->barrier_word, h->barrier_word, 1, ncclInt, ncclMax, (ncclComm_t)h->nccl_comm, h->stream));
+  return CHAN_OK;
+}
+
 // statistics profiles: replaces MPI_Allreduce(SUM) of fft.c:260
 int allreduce_sum_host(chan_handle* h, double* dev_buf, int n) {
   if (h->cfg.size > 1) CHAN_NCCL(h, ncclAllReduce(dev_buf, dev_buf, n, ncclDouble, ncclSum, (ncclComm_t)h->nccl_comm, h->stream));

@@ -19,6 +19,7 @@
 // Traffic per substep (P = one compact field): pre 3P + 5P, post 7P + 6P + 1P of pivots, pivots
 // 0.5P written: 22.5P against 55P of the scratch version; parallelism x nseg (25 at NY = 193).
 #include <vector>
+#include <string.h>
 #include "pencil_common.cuh"
 
 namespace chan {
@@ -254,7 +255,7 @@ __device__ __forceinline__ bool setup_seg(const PArgs<T>& a, int cb, Mode& md, W
 
 // =================================================================================
 template <typename T, int S, int CB>
-__global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st) {
+__global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st, PeerOut po) {
   typedef typename Vec2<T>::type T2;
   extern __shared__ double sm_seg[];
   Mode md; Wave<T> wv; Ctx c;
@@ -262,18 +263,18 @@ __global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, Seg
   const long stp = 2 * a.M; const int cc = md.c;
   const bool with_mean = md.zero_mode && a.use_mean;
   double f[2][S];
-  T uu[S], ww[S], upp[S], wpp[S], vp[S];
+  T uu[S], ww[S], upp[S], wpp[S], vp[S], vo[S];
 #pragma unroll
   for (int r = 0; r < S; r++) {
     int j = c.j0 + r;
-    uu[r] = ww[r] = upp[r] = wpp[r] = vp[r] = 0;
+    uu[r] = ww[r] = upp[r] = wpp[r] = vp[r] = vo[r] = 0;
     if (j < c.ny) {
       long cm = (long)j * a.M + md.m;
       T2 dvz = a.dv[cm], gz = a.g[cm];
       uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, cc, uu[r], ww[r]);
       uw_comp<T, T2>(wv, md, md.zero_mode, dvz, gz, cc ^ 1, upp[r], wpp[r]);
       if (with_mean) { uu[r] = cc ? (T)0 : a.mean_u[j]; upp[r] = cc ? a.mean_u[j] : (T)0; }   // writeUmean (nonLinear.c:19-21)
-      vp[r] = other<T2, T>(a.v[cm], cc);
+      { T2 vz = a.v[cm]; vp[r] = other<T2, T>(vz, cc); vo[r] = own<T2, T>(vz, cc); }
     }
     f[0][r] = (double)uu[r]; f[1][r] = (double)ww[r];
   }
@@ -285,10 +286,22 @@ __global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, Seg
     if (j < c.ny) {
       long re = (long)j * stp + md.e;
       T dudy = (T)f[0][r], dwdy = (T)f[1][r], s = wv.sc;
-      ((T*)a.u)[re] = uu[r]; ((T*)a.w)[re] = ww[r];
-      ((T*)a.ox)[re] = dwdy - s * wv.k3 * vp[r];                  // omega_x = dw/dy - i k3 v
-      ((T*)a.oy)[re] = s * (wv.k3 * upp[r] - wv.k1 * wpp[r]);     // omega_y = i (k3 u - k1 w)
-      ((T*)a.oz)[re] = -dudy + s * wv.k1 * vp[r];                 // omega_z = -du/dy + i k1 v
+      T o1 = dwdy - s * wv.k3 * vp[r];                  // omega_x = dw/dy - i k3 v
+      T o2 = s * (wv.k3 * upp[r] - wv.k1 * wpp[r]);     // omega_y = i (k3 u - k1 w)
+      T o3 = -dudy + s * wv.k1 * vp[r];                 // omega_z = -du/dy + i k1 v
+      if (po.nranks > 1) {
+        // multi-GPU: row j goes straight into the receive buffer of the rank that owns plane j (NVLink
+        // store for the other ranks) — this IS the pencil -> plane transpose of channel_cuda_mpi.c:95-128
+        int p = 0;
+#pragma unroll
+        for (int i = 1; i < 8; i++) p += (i < po.nranks && j >= po.part_j[i]) ? 1 : 0;
+        long idx = 2 * (po.src_off[p] + (long)(j - po.part_j[p]) * a.M) + md.e;
+        ((T*)po.rcv[p][0])[idx] = uu[r]; ((T*)po.rcv[p][1])[idx] = vo[r]; ((T*)po.rcv[p][2])[idx] = ww[r];
+        ((T*)po.rcv[p][3])[idx] = o1; ((T*)po.rcv[p][4])[idx] = o2; ((T*)po.rcv[p][5])[idx] = o3;
+      } else {
+        ((T*)a.u)[re] = uu[r]; ((T*)a.w)[re] = ww[r];
+        ((T*)a.ox)[re] = o1; ((T*)a.oy)[re] = o2; ((T*)a.oz)[re] = o3;
+      }
       if (md.zero_mode && cc == 0 && a.sc) {                      // readUtau (convolution.c:14-16)
         if (j == 0) a.sc->dudy_wall[0] = (double)dudy;
         if (j == c.ny - 1) a.sc->dudy_wall[1] = (double)dudy;
@@ -488,7 +501,16 @@ static int launch_seg(chan_handle* h, bool post, int n) {
     pencil_post_seg_kernel<T, S, CB><<<grid, block, sm, h->stream>>>(a, st);
   } else {
     CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    pencil_pre_seg_kernel<T, S, CB><<<grid, block, sm, h->stream>>>(a, st);
+    PeerOut po; memset(&po, 0, sizeof(po));
+    po.nranks = h->peer_ready ? h->cfg.size : 1;
+    if (h->peer_ready) {
+      for (int p = 0; p <= h->cfg.size; p++) po.part_j[p] = h->part_j[p];
+      for (int p = 0; p < h->cfg.size; p++) {
+        po.src_off[p] = (long)(h->part_j[p + 1] - h->part_j[p]) * h->d.ikx0 * h->d.Kz;
+        for (int f = 0; f < 6; f++) po.rcv[p][f] = h->peer_rcv[p][f];
+      }
+    }
+    pencil_pre_seg_kernel<T, S, CB><<<grid, block, sm, h->stream>>>(a, st, po);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());

@@ -29,8 +29,8 @@ using namespace fft;
 template <typename T>
 struct XArgs {
   typedef typename Vec2<T>::type T2;
-  const T2* src[6]; T2* dst[6];   // plane-side field buffers (see SegMap)
-  SegMap seg; int j_glob0;        // global index of local plane 0 (export only)
+  const T2* src[6]; SegDst<typename Vec2<T>::type> dst[3];   // plane-side field buffers (see SegMap)
+  SegMap seg, seg_out; int j_glob0;        // global index of local plane 0 (export only)
   T2* Q;                          // [f][pb][NX][Kz]
   FftPlan px;
   int nx, Kx, Kz, kxmax, j_start, pb; long M;
@@ -67,11 +67,10 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   if (a.dbg_skip & 2) return;
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  T2* dst = a.dst[f];
   FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
   for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, dst, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
 // -------------------------------------------------------------------------------
@@ -199,7 +198,8 @@ template <typename T>
 static void fill_x(chan_handle* h, XArgs<T>& a) {
   typedef typename Vec2<T>::type T2;
   a.Q = (T2*)h->Q; a.px = h->px; a.nx = h->d.nx; a.Kx = h->d.Kx; a.Kz = h->d.Kz; a.kxmax = h->d.kxmax;
-  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0; a.dbg_skip = h->tune.x_skip; a.seg = h->seg; a.j_glob0 = h->d.j0;
+  a.M = (long)h->d.Kx * h->d.Kz; a.scale = (T)0; a.dbg_skip = h->tune.x_skip; a.seg = h->seg; a.seg_out = h->seg; a.j_glob0 = h->d.j0;
+  for (int f = 0; f < 3; f++) for (int g = 0; g < 8; g++) a.dst[f].p[g] = 0;
 }
 template <typename T>
 static void fill_z(chan_handle* h, ZArgs<T>& a) {
@@ -210,18 +210,28 @@ static void fill_z(chan_handle* h, ZArgs<T>& a) {
   a.phys = 0; a.XP = 1; a.SS = 0; a.dbg_stop = h->tune.z_stop; a.j_glob0 = h->d.j0;
 }
 
+// forward stores go straight into the owners' pencil-side fields: segment g = rank g, rows are global
+template <typename T>
+static void peer_out(chan_handle* h, XArgs<T>& xf) {
+  typedef typename Vec2<T>::type T2;
+  for (int g = 0; g < h->cfg.size; g++) {
+    xf.seg_out.base[g] = (long)h->d.j0 * xf.seg_out.width[g] * h->d.Kz;
+    for (int f = 0; f < 3; f++) xf.dst[f].p[g] = (T2*)h->peer_H[g][f];
+  }
+}
+
 template <typename T>
 static int nonlinear_t(chan_handle* h) {
   typedef typename Vec2<T>::type T2;
   XArgs<T> xi, xf; fill_x(h, xi); fill_x(h, xf);
   void* pin[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
   void* pout[3] = { h->ox, h->oy, h->oz };
-  const bool multi = h->cfg.size > 1;
-  if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
-  const void* in[6]; void* out[3];
-  for (int f = 0; f < 6; f++) in[f] = multi ? h->rcv[f] : pin[f];
-  for (int f = 0; f < 3; f++) out[f] = multi ? h->snd[f] : pout[f];
-  for (int f = 0; f < 6; f++) { xi.src[f] = (const T2*)in[f]; xi.dst[f] = 0; xf.src[f] = 0; xf.dst[f] = f < 3 ? (T2*)out[f] : 0; }
+  const bool multi = h->cfg.size > 1, peer = multi && h->peer_ready;
+  if (peer) { int rc = stream_barrier(h); if (rc) return rc; }                 // every rank's `pre` has delivered
+  else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
+  for (int f = 0; f < 6; f++) xi.src[f] = (const T2*)(multi ? h->rcv[f] : pin[f]);
+  for (int f = 0; f < 3; f++) for (int g = 0; g < 8; g++) xf.dst[f].p[g] = (T2*)(multi ? h->snd[f] : pout[f]);
+  if (peer) peer_out<T>(h, xf);
   ZArgs<T> z; fill_z(h, z);
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
@@ -234,7 +244,8 @@ static int nonlinear_t(chan_handle* h) {
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
     timing_end(h, t);
   }
-  if (multi) { int rc = allreduce_umax(h); if (rc) return rc; rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
+  if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer stores
+  if (multi && !peer) { int rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
   return CHAN_OK;
 }
 
@@ -242,12 +253,12 @@ template <typename T>
 static int symmetrize_t(chan_handle* h, void* fa, void* fb) {
   typedef typename Vec2<T>::type T2;
   XArgs<T> xi, xf; fill_x(h, xi); fill_x(h, xf);
-  for (int f = 0; f < 6; f++) { xi.src[f] = 0; xi.dst[f] = 0; xf.src[f] = 0; xf.dst[f] = 0; }
+  for (int f = 0; f < 6; f++) { xi.src[f] = 0; xf.src[f] = 0; }
   void* pf[2] = { fa, fb };
   const bool multi = h->cfg.size > 1;
   if (multi) { int rc = exchange_to_planes(h, 2, pf); if (rc) return rc; }
   xi.src[0] = (const T2*)(multi ? h->rcv[0] : fa); xi.src[1] = (const T2*)(multi ? h->rcv[1] : fb);
-  xf.dst[0] = (T2*)(multi ? h->snd[0] : fa); xf.dst[1] = (T2*)(multi ? h->snd[1] : fb);
+  for (int g = 0; g < 8; g++) { xf.dst[0].p[g] = (T2*)(multi ? h->snd[0] : fa); xf.dst[1].p[g] = (T2*)(multi ? h->snd[1] : fb); }
   xf.scale = (T)(h->d.nx * h->d.nzp);
   ZArgs<T> z; fill_z(h, z);
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
@@ -266,7 +277,7 @@ static int export_t(chan_handle* h, const void* f, void* phys) {
   typedef typename Vec2<T>::type T2;
   if (h->cfg.size > 1) return set_err(h, CHAN_ERR_STATE, "chan_fft_backward_transpose is a single-GPU validation entry point");
   XArgs<T> xi; fill_x(h, xi);
-  for (int k = 0; k < 6; k++) { xi.src[k] = 0; xi.dst[k] = 0; }
+  for (int k = 0; k < 6; k++) xi.src[k] = 0;
   xi.src[0] = (const T2*)f;
   ZArgs<T> z; fill_z(h, z); z.phys = (T*)phys;
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {

@@ -28,12 +28,19 @@ template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
   return q;
 }
 
-FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz) {
+FFT_HD int seg_index(const SegMap& sm, int ikx) {
   int sg = 0;
 #pragma unroll
   for (int i = 1; i < 8; i++) sg += (i < sm.nseg && ikx >= sm.start[i]) ? 1 : 0;
+  return sg;
+}
+FFT_HD size_t seg_offset_in(const SegMap& sm, int sg, int jl, int ikx, int Kz) {
   return (size_t)sm.base[sg] + ((size_t)jl * sm.width[sg] + (ikx - sm.start[sg])) * Kz;
 }
+FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz) { return seg_offset_in(sm, seg_index(sm, ikx), jl, ikx, Kz); }
+// destination of the forward store: one base pointer per kx segment (= per destination rank when the
+// store goes straight into the peers' pencil-side fields over NVLink; all equal otherwise)
+template <class T2> struct SegDst { T2* p[8]; };
 
 // =================================== x direction =================================================
 // shared layout: s[pos*TK + t], t = kz within the tile (batch-fastest: conflict-free at every stride)
@@ -95,7 +102,7 @@ FFT_HD void x_fwd_load_first(T2* s, const T2* q, const PlanT<T2>& pl, int TK, in
 }
 // forward, stage 0 (m = 1) fused with the truncating store into the compact spectral rows
 template <class T2, int R>
-FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const SegMap& sm, int jl, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax,
+FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap& sm, int jl, const PlanT<T2>& pl, int TK, int kz0, int Kz, int Kx, int kxmax,
                                typename RealOf<T2>::type scale, int tid, int nthr) {
   const int n = pl.n, ng = n / R;
   for (int b = tid; b < ng * TK; b += nthr) {
@@ -112,7 +119,8 @@ FFT_HD void x_fwd_stage0_store(const T2* s, T2* dst, const SegMap& sm, int jl, c
         if (ikx >= 0) {
           T2 v = a[p];
           if (scale != 0) { v.x /= scale; v.y /= scale; }
-          dst[seg_offset(sm, jl, ikx, Kz) + kz] = v;
+          int sg = seg_index(sm, ikx);
+          dst.p[sg][seg_offset_in(sm, sg, jl, ikx, Kz) + kz] = v;
         }
       }
     }

@@ -152,6 +152,17 @@ int chan_fft_backward_transpose(chan_handle* h, const void* u_dev, void* phys_de
  * the array, so calls that may overlap on the GPU must be serialised by the caller. */
 int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_pencils);
 
+/* ---- multi-GPU peer-store exchange (no counterpart in the reference, which stages every transpose
+ * through host memory and MPI_Alltoall, channel_cuda_mpi.c:75-85) ------------------------------
+ * One process per GPU: chan_ipc_export writes CHAN_IPC_BYTES bytes describing this rank's exchange
+ * buffers; the host passes them to every other rank (any transport: the python launcher uses
+ * torch.distributed), which calls chan_ipc_import(h, rank_of_owner, bytes).  Once every peer has been
+ * imported the substep stores exchanged fields straight into the owners' buffers over NVLink from
+ * inside the producing kernels, and NCCL only provides two stream-ordered barriers per substep. */
+#define CHAN_IPC_BYTES (9 * 64)
+int chan_ipc_export(chan_handle* h, void* bytes_out);
+int chan_ipc_import(chan_handle* h, int peer_rank, const void* bytes_in);
+
 /* ---- slab decomposition (main.c:47, channel.h:71-79), pure host arithmetic --- */
 /* splits n items over `size` ranks as evenly as possible: [*start, *start+*count) */
 int chan_partition(int n, int size, int rank, int* start, int* count);

@@ -54,10 +54,11 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   }
   double e1 = sqrt(err / nrm);
   // forward of the physical lines must give back nx * src on the active modes
+  SegDst<T2> dsts; for (int i = 0; i < 8; i++) dsts.p[i] = dst.data();
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
     for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, t, TK, TK, TK, TK, tid, NTHR);
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s.data(), dst.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
   }
   err = nrm = 0;
   for (int i = 0; i < Kx; i++) for (int kz = 0; kz < Kz; kz++) { size_t o = at(i, kz); err += std::norm(cd(dst[o].x - src[o].x, dst[o].y - src[o].y)); nrm += std::norm(cd(src[o].x, src[o].y)); }
