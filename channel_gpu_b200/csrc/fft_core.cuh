@@ -122,24 +122,32 @@ template <int R, int SIGN, class T2> FFT_HD void apply_twiddles(T2* a, const T2*
 }
 
 // ---- a whole shared-memory stage ----------------------------------------------------------------
-// element (pos, line) lives at s[pos*st + line_index(l)], line_index(l) = (l / nact) * nper + l % nact
-// (nact of every nper interleaved lines take part; nlines = number of participating lines)
+// element (row, line) lives at s[row*st + skew(row) + line_index(l)], line_index(l) = (l / nact) * nper + l % nact
+// (nact of every nper interleaved lines take part; nlines = number of participating lines).
+// skew(row) = row / sk for sk > 0 (z transforms: one extra element every r_0 rows, so that rows that differ
+// in the HIGH digits of the digit-reversed position fall into different banks, see z_unpack_store), 0 for sk = 0.
+// sk divides the span m of every stage but the m = 1 stage, where all rows of a butterfly share one skew.
+FFT_HD int skew_of(int row, int sk, float rsk) { return sk ? (int)(((float)row + 0.5f) * rsk) : 0; }
+
 template <class T2, int R, int SIGN, bool DIT>
-FFT_HD void smem_stage(T2* s, int n, int m, int st, int nlines, int nact, int nper, const T2* tw, int tid, int nthr) {
+FFT_HD void smem_stage(T2* s, int n, int m, int st, int nlines, int nact, int nper, const T2* tw, int tid, int nthr, int sk = 0) {
   const int nb = n / R, tws = n / (m * R);
+  const float rsk = sk ? 1.0f / (float)sk : 0.0f;
+  const int qst = m * st + ((sk && m >= sk) ? m / sk : 0);
   for (int b = tid; b < nb * nlines; b += nthr) {
     int l = b % nlines, bf = b / nlines;
     int li = (l / nact) * nper + l % nact;
     int g = bf / m, k = bf - g * m;
-    T2* p = s + (size_t)(g * m * R + k) * st + li;
+    const int row0 = g * m * R + k;
+    T2* p = s + (size_t)row0 * st + skew_of(row0, sk, rsk) + li;
     T2 a[R];
 #pragma unroll
-    for (int q = 0; q < R; q++) a[q] = p[(size_t)q * m * st];
+    for (int q = 0; q < R; q++) a[q] = p[(size_t)q * qst];
     if (DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
     Dft<R, SIGN, T2>::run(a);
     if (!DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
 #pragma unroll
-    for (int q = 0; q < R; q++) p[(size_t)q * m * st] = a[q];
+    for (int q = 0; q < R; q++) p[(size_t)q * qst] = a[q];
   }
 }
 

@@ -121,6 +121,71 @@ struct ElimVar {
   }
 };
 
+// ---- pointer-walking variants used by pencil_post: address arithmetic was 48 % of its instructions
+// (profiles/r01_final_*).  `cur` points at this chain's scratch element of the CURRENT sweep row, `ss` is
+// the pointer step of one sweep position (+row stride going up, -row stride going down).
+struct ElimD1P {
+  double f1, f2, dprev;
+  __device__ __forceinline__ void step(const D1Tab& t, int jj, int ny, double f, double* cur, long ss) {
+    if (jj == 0) { f2 = f; return; }
+    if (jj == 1) { f1 = f; return; }
+    if (jj == 2) {
+      double d0 = __ldg(t.eC) * f2 + __ldg(t.eN) * f1 + __ldg(t.eP) * f;
+      cur[-2 * ss] = d0; dprev = d0;
+    }
+    const int r = jj - 1;
+    double d = __ldg(t.eP + r) * f2 + __ldg(t.eC + r) * f1 + __ldg(t.eN + r) * f - __ldg(t.eL + r) * dprev;
+    cur[-ss] = d; dprev = d;
+    if (jj == ny - 1) {
+      double dl = __ldg(t.eC + jj) * f + __ldg(t.eP + jj) * f1 + __ldg(t.eN + jj) * f2 - __ldg(t.eL + jj) * dprev;
+      cur[0] = dl;
+    }
+    f2 = f1; f1 = f;
+  }
+};
+template <int NR>
+struct ElimVarP {
+  double f1[NR], f2[NR], dprev[NR], cprev;
+  // cur[q]: scratch element of the current sweep row; pcur: pivot element of the current sweep row (step ps)
+  __device__ __forceinline__ void step(const D2Tab& t, int jj, int ny, const double (&f)[NR], bool implicit, double kk, double D,
+                                       double* const (&cur)[NR], long ss, double* pcur, long ps) {
+    if (jj == 0) {
+#pragma unroll
+      for (int q = 0; q < NR; q++) f2[q] = f[q];
+      return;
+    }
+    if (jj == 1) {
+#pragma unroll
+      for (int q = 0; q < NR; q++) { f1[q] = f[q]; cur[q][-ss] = 0.0; dprev[q] = 0.0; }
+      pcur[-ps] = 0.0; cprev = 0.0;
+      return;
+    }
+    const int r = jj - 1;
+    double rP = __ldg(t.rP + r), rN = __ldg(t.rN + r);
+    double wP = __ldg(t.wP + r), wC = __ldg(t.wC + r), wN = __ldg(t.wN + r);
+    double lo, di, up;
+    if (implicit) { lo = rP - D * wP + D * kk * rP; di = 1.0 - D * wC + D * kk * 1.0; up = rN - D * wN + D * kk * rN; }
+    else          { lo = wP - kk * rP;              di = wC - kk;                     up = wN - kk * rN; }
+    if (r == 1) lo = 0.0;
+    if (r == ny - 2) up = 0.0;
+    double piv = 1.0 / (di - lo * cprev);
+    double cp = up * piv;
+#pragma unroll
+    for (int q = 0; q < NR; q++) {
+      double rhs = rN * f[q] + f1[q] + rP * f2[q];
+      double d = (rhs - lo * dprev[q]) * piv;
+      cur[q][-ss] = d; dprev[q] = d;
+      f2[q] = f1[q]; f1[q] = f[q];
+    }
+    pcur[-ps] = cp; cprev = cp;
+    if (jj == ny - 1) {
+#pragma unroll
+      for (int q = 0; q < NR; q++) cur[q][0] = 0.0;
+      pcur[0] = 0.0;
+    }
+  }
+};
+
 // ---- unfused building blocks (operator-level API, calcVdV) -------------------
 // out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
 template <typename T>
@@ -166,17 +231,20 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   double det = q.dv1 * p.dv2 - p.dv1 * q.dv2;
   double c1 = p.dv2 * dvm - q.dv2 * dvp; c1 = -c1 / det;
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
-  const Prefetch pf(ny);
+  T* pp = phi + md.e; T* pv = v + md.e; T* pd = dv + md.e;
+  const double* yt = a.yt.y;
+  T pc = *pp, vc = *pv, dc = *pd;
   for (int j = 0; j < ny; j++) {
-    long i = (long)j * st + md.e;
-    pf(phi + i, st, j, 1); pf(v + i, st, j, 1); pf(dv + i, st, j, 1);
-    BcFun f = bc_functions(k, __ldg(a.yt.y + j), md.c);
-    double pp = (double)phi[i], vv = (double)v[i], dd = (double)dv[i];
-    pp = pp + c1 * f.ddv1 + c2 * f.ddv2;
+    T pn = pc, vn = vc, dn = dc;
+    if (j + 1 < ny) { pn = pp[st]; vn = pv[st]; dn = pd[st]; }
+    BcFun f = bc_functions(k, __ldg(yt), md.c);
+    double ppv = (double)pc, vv = (double)vc, dd = (double)dc;
+    ppv = ppv + c1 * f.ddv1 + c2 * f.ddv2;
     dd = dd + c1 * f.dv1 + c2 * f.dv2;
     vv = vv + c1 * f.v1 + c2 * f.v2;
-    if (md.zero_mode) { pp = 0.0; vv = 0.0; dd = 0.0; }
-    phi[i] = (T)pp; v[i] = (T)vv; dv[i] = (T)dd;
+    if (md.zero_mode) { ppv = 0.0; vv = 0.0; dd = 0.0; }
+    *pp = (T)ppv; *pv = (T)vv; *pd = (T)dd;
+    pc = pn; vc = vn; dc = dn; pp += st; pv += st; pd += st; yt++;
   }
 }
 
@@ -269,74 +337,71 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   Mode md; Wave<T> wv;
   if (!setup(a, md, wv)) return;
-  const long st = 2 * a.M; const int ny = a.ny; const int c = md.c; const long e = md.e;
+  const long st = 2 * a.M, M = a.M; const int ny = a.ny; const int c = md.c; const long e = md.e;
   const T dt = (T)a.sc->dt;
   const T s = wv.sc;
-  const T* phiR = (const T*)a.phi; const T* gR = (const T*)a.g;
-  const T2* H1 = a.ox; const T2* H3 = a.oz; const T* H2R = (const T*)a.oy;
-  const Prefetch pf(ny);
-  // Every pass keeps two rows in flight: the loads of the next row are issued before the current
-  // row is computed (the sweeps are latency-bound: one dependent row per thread otherwise).
+  const long top = (long)(ny - 1);
+  // Every pass walks its arrays with running pointers (rows are `st` reals / `M` complex apart) and keeps
+  // two rows in flight: the loads of the next row are issued before the current row is computed.
   // P1 (up): eliminate d/dy of phi, g and hv = -i (k1 H1 + k3 H3)  (calcHvgkernel, nonLinear_kernels.cu:129-130)
   {
-    ElimD1 ep, eg, eh;
-    T2 h1 = H1[md.m], h3 = H3[md.m]; T p = phiR[e], g = gR[e];
+    ElimD1P ep, eg, eh;
+    const T2* pH1 = a.ox + md.m; const T2* pH3 = a.oz + md.m;
+    const T* pp = (const T*)a.phi + e; const T* pg = (const T*)a.g + e;
+    double* sa = a.sA + e; double* sb = a.sB + e; double* sc = a.sC + e;
+    T2 h1 = *pH1, h3 = *pH3; T p = *pp, g = *pg;
     for (int j = 0; j < ny; j++) {
-      long cm = (long)j * a.M + md.m, re = (long)j * st + e;
-      pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
       T2 h1n = h1, h3n = h3; T pn = p, gn = g;
-      if (j + 1 < ny) { h1n = H1[cm + a.M]; h3n = H3[cm + a.M]; pn = phiR[re + st]; gn = gR[re + st]; }
+      if (j + 1 < ny) { h1n = pH1[M]; h3n = pH3[M]; pn = pp[st]; gn = pg[st]; }
       T h1p = other<T2, T>(h1, c), h3p = other<T2, T>(h3, c);
       T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
-      ep.step(a.yt.d1[0], 0, j, ny, (double)p, a.sA, st, e);
-      eg.step(a.yt.d1[0], 0, j, ny, (double)g, a.sB, st, e);
-      eh.step(a.yt.d1[0], 0, j, ny, (double)hv, a.sC, st, e);
+      ep.step(a.yt.d1[0], j, ny, (double)p, sa, st);
+      eg.step(a.yt.d1[0], j, ny, (double)g, sb, st);
+      eh.step(a.yt.d1[0], j, ny, (double)hv, sc, st);
       h1 = h1n; h3 = h3n; p = pn; g = gn;
+      pH1 += M; pH3 += M; pp += st; pg += st; sa += st; sb += st; sc += st;
     }
   }
   // P2 (down): phi', g', hv' ; eliminate d/dy of phi', g' (second derivative = d/dy twice, Q4)
   {
-    ElimD1 ep, eg;
+    ElimD1P ep, eg;
     double xp = 0.0, xg = 0.0, xh = 0.0;
-    long re0 = (long)(ny - 1) * st + e;
-    double dA = a.sA[re0], dB = a.sB[re0], dC = a.sC[re0];
+    double* sa = a.sA + top * st + e; double* sb = a.sB + top * st + e; double* sc = a.sC + top * st + e;
+    const double* cpt = a.yt.d1[0].cp + top;
+    double dA = *sa, dB = *sb, dC = *sc;
     for (int jj = 0; jj < ny; jj++) {
-      int j = ny - 1 - jj; long re = (long)j * st + e;
-      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sC + re, st, j, -1);
       double dAn = dA, dBn = dB, dCn = dC;
-      if (j > 0) { dAn = a.sA[re - st]; dBn = a.sB[re - st]; dCn = a.sC[re - st]; }
-      double cp = __ldg(a.yt.d1[0].cp + j);
+      if (jj + 1 < ny) { dAn = sa[-st]; dBn = sb[-st]; dCn = sc[-st]; }
+      double cp = __ldg(cpt);
       xp = dA - cp * xp; xg = dB - cp * xg; xh = dC - cp * xh;
-      a.sC[re] = rnd<T>(xh);
-      ep.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xp), a.sA, st, e);
-      eg.step(a.yt.d1[1], 1, jj, ny, rnd<T>(xg), a.sB, st, e);
+      *sc = rnd<T>(xh);
+      ep.step(a.yt.d1[1], jj, ny, rnd<T>(xp), sa, -st);
+      eg.step(a.yt.d1[1], jj, ny, rnd<T>(xg), sb, -st);
       dA = dAn; dB = dBn; dC = dCn;
+      sa -= st; sb -= st; sc -= st; cpt--;
     }
   }
   // P3 (up): phi'', g'' -> explicit RK update (rk_step_1/2, RK3_kernels.cu:76-80,138-142) -> eliminate implicit solves
   const double bdt = (double)(dt * a.betha);                         // dt*betha in the state type (:235)
   const double Dimp = a.nuD * bdt;
   {
-    ElimVar<2> ev;
-    double* const ss[2] = { a.sA, a.sB };
+    ElimVarP<2> ev;
     double xp = 0.0, xg = 0.0;
-    const T* RpR = (const T*)a.Rphi; const T* RgR = (const T*)a.Rg;
+    double* sa = a.sA + e; double* sb = a.sB + e; const double* sc = a.sC + e; double* sp = a.sP + md.m;
+    const T2* pH1 = a.ox + md.m; const T2* pH3 = a.oz + md.m; const T* pH2 = (const T*)a.oy + e;
+    const T* pp = (const T*)a.phi + e; const T* pg = (const T*)a.g + e;
+    T* pRp = (T*)a.Rphi + e; T* pRg = (T*)a.Rg + e;
+    const double* cpt = a.yt.d1[1].cp + top;
     struct Row { double dA, dB, dC; T2 h1, h3; T h2, p, g, rp, rg; };
     Row r;
-    r.dA = a.sA[e]; r.dB = a.sB[e]; r.dC = a.sC[e]; r.h1 = H1[md.m]; r.h3 = H3[md.m];
-    r.h2 = H2R[e]; r.p = phiR[e]; r.g = gR[e]; r.rp = RpR[e]; r.rg = RgR[e];
+    r.dA = *sa; r.dB = *sb; r.dC = *sc; r.h1 = *pH1; r.h3 = *pH3; r.h2 = *pH2; r.p = *pp; r.g = *pg; r.rp = *pRp; r.rg = *pRg;
     for (int j = 0; j < ny; j++) {
-      long cm = (long)j * a.M + md.m, re = (long)j * st + e;
-      pf(a.sA + re, st, j, 1); pf(a.sB + re, st, j, 1); pf(a.sC + re, st, j, 1);
-      pf(H1 + cm, a.M, j, 1); pf(H3 + cm, a.M, j, 1); pf(H2R + re, st, j, 1);
-      pf(phiR + re, st, j, 1); pf(gR + re, st, j, 1);
-      pf(RpR + re, st, j, 1); pf(RgR + re, st, j, 1);
       Row n = r;
       if (j + 1 < ny) {
-        n.dA = a.sA[re + st]; n.dB = a.sB[re + st]; n.dC = a.sC[re + st]; n.h1 = H1[cm + a.M]; n.h3 = H3[cm + a.M];
-        n.h2 = H2R[re + st]; n.p = phiR[re + st]; n.g = gR[re + st]; n.rp = RpR[re + st]; n.rg = RgR[re + st];
+        n.dA = sa[st]; n.dB = sb[st]; n.dC = sc[st]; n.h1 = pH1[M]; n.h3 = pH3[M];
+        n.h2 = pH2[st]; n.p = pp[st]; n.g = pg[st]; n.rp = pRp[st]; n.rg = pRg[st];
       }
-      double cp = __ldg(a.yt.d1[1].cp + (ny - 1 - j));
+      double cp = __ldg(cpt);
       xp = r.dA - cp * xp; xg = r.dB - cp * xg;
       T pyy = (T)xp, gyy = (T)xg;
       T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
@@ -346,63 +411,69 @@ __global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
       T gw = r.g + dt * (a.alpha * a.nuT * (gyy - wv.kk * r.g) + a.dseda * r.rg);
       pw = pw + dt * a.gammad * rp_new;
       gw = gw + dt * a.gammad * rg_new;
-      ((T*)a.Rphi)[re] = rp_new; ((T*)a.Rg)[re] = rg_new;
+      *pRp = rp_new; *pRg = rg_new;
       const double f[2] = { (double)pw, (double)gw };
-      ev.step(a.yt.d2[0], 0, j, ny, f, true, wv.kkd, Dimp, ss, st, e, a.sP, a.M, md.m);
+      double* const cur[2] = { sa, sb };
+      ev.step(a.yt.d2[0], j, ny, f, true, wv.kkd, Dimp, cur, st, sp, M);
       r = n;
+      sa += st; sb += st; sc += st; sp += M; pH1 += M; pH3 += M; pH2 += st; pp += st; pg += st; pRp += st; pRg += st; cpt--;
     }
   }
   // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new
   {
-    ElimVar<1> eh;
-    double* const ss[1] = { a.sA };
+    ElimVarP<1> eh;
     double xp = 0.0, xg = 0.0;
-    long re0 = (long)(ny - 1) * st + e;
-    double dA = a.sA[re0], dB = a.sB[re0], cp = a.sP[(long)(ny - 1) * a.M + md.m];
+    double* sa = a.sA + top * st + e; const double* sb = a.sB + top * st + e; double* sp = a.sP + top * M + md.m;
+    T* pp = (T*)a.phi + top * st + e; T* pg = (T*)a.g + top * st + e;
+    double dA = *sa, dB = *sb, cp = *sp;
     for (int jj = 0; jj < ny; jj++) {
-      int j = ny - 1 - jj; long re = (long)j * st + e;
-      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.sP + (long)j * a.M + md.m, a.M, j, -1);
       double dAn = dA, dBn = dB, cpn = cp;
-      // rows below j are still the implicit-solve data: the Helmholtz elimination lags one row ABOVE
-      if (j > 0) { dAn = a.sA[re - st]; dBn = a.sB[re - st]; cpn = a.sP[(long)(j - 1) * a.M + md.m]; }
+      // rows below are still the implicit-solve data: the Helmholtz elimination lags one row ABOVE
+      if (jj + 1 < ny) { dAn = sa[-st]; dBn = sb[-st]; cpn = sp[-M]; }
       xp = dA - cp * xp; xg = dB - cp * xg;
       // both components of a mode share the pivot row: every lane must have read its pivots before
-      // any lane overwrites row j+1 with the Helmholtz pivot of the lagging row
+      // any lane overwrites the row above with the Helmholtz pivot of the lagging row
       __syncwarp();
-      ((T*)a.g)[re] = (T)xg;
-      ((T*)a.phi)[re] = (T)xp;
+      *pg = (T)xg;
+      *pp = (T)xp;
       const double f[1] = { rnd<T>(xp) };
-      eh.step(a.yt.d2[1], 1, jj, ny, f, false, wv.kkd, 0.0, ss, st, e, a.sP, a.M, md.m);
+      double* const cur[1] = { sa };
+      eh.step(a.yt.d2[1], jj, ny, f, false, wv.kkd, 0.0, cur, -st, sp, -M);
       dA = dAn; dB = dBn; cp = cpn;
+      sa -= st; sb -= st; sp -= M; pp -= st; pg -= st;
     }
   }
   // P5 (up): v ; eliminate d/dy v
   {
-    ElimD1 ev;
+    ElimD1P ev;
     double xv = 0.0;
-    double dA = a.sA[e], cp = a.sP[md.m];
+    double* sa = a.sA + e; const double* sp = a.sP + md.m; T* pv = (T*)a.v + e;
+    double dA = *sa, cp = *sp;
     for (int j = 0; j < ny; j++) {
-      long re = (long)j * st + e;
-      pf(a.sA + re, st, j, 1); pf(a.sP + (long)j * a.M + md.m, a.M, j, 1);
       double dAn = dA, cpn = cp;
-      if (j + 1 < ny) { dAn = a.sA[re + st]; cpn = a.sP[(long)(j + 1) * a.M + md.m]; }
+      if (j + 1 < ny) { dAn = sa[st]; cpn = sp[M]; }
       xv = dA - cp * xv;
-      ((T*)a.v)[re] = (T)xv;
-      ev.step(a.yt.d1[0], 0, j, ny, rnd<T>(xv), a.sA, st, e);
+      *pv = (T)xv;
+      ev.step(a.yt.d1[0], j, ny, rnd<T>(xv), sa, st);
       dA = dAn; cp = cpn;
+      sa += st; sp += M; pv += st;
     }
   }
   // P6 (down): dv
   double dvm = 0.0, dvp = 0.0;
   {
     double x = 0.0;
+    const double* sa = a.sA + top * st + e; T* pdv = (T*)a.dv + top * st + e;
+    const double* cpt = a.yt.d1[0].cp + top;
+    double dA = *sa;
     for (int j = ny - 1; j >= 0; j--) {
-      long re = (long)j * st + e;
-      pf(a.sA + re, st, j, -1);
-      x = a.sA[re] - __ldg(a.yt.d1[0].cp + j) * x;
-      ((T*)a.dv)[re] = (T)x;
+      double dAn = dA;
+      if (j > 0) dAn = sa[-st];
+      x = dA - __ldg(cpt) * x;
+      *pdv = (T)x;
       if (j == ny - 1) dvp = rnd<T>(x);
       if (j == 0) dvm = rnd<T>(x);
+      dA = dAn; sa -= st; pdv -= st; cpt--;
     }
   }
   // P7: wall correction (skipped when dt <= 1e-8, including the zeroing of mode (0,0))

@@ -254,8 +254,8 @@ __device__ __forceinline__ bool setup_seg(const PArgs<T>& a, int cb, Mode& md, W
 }
 
 // =================================================================================
-template <typename T, int S, int CB>
-__global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st, PeerOut po) {
+template <typename T, int S, int CB, int MINB>
+__global__ void __launch_bounds__(CB * 32, MINB) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st, PeerOut po) {
   typedef typename Vec2<T>::type T2;
   extern __shared__ double sm_seg[];
   Mode md; Wave<T> wv; Ctx c;
@@ -311,8 +311,8 @@ __global__ void __launch_bounds__(CB * 32) pencil_pre_seg_kernel(PArgs<T> a, Seg
 }
 
 // =================================================================================
-template <typename T, int S, int CB>
-__global__ void __launch_bounds__(CB * 32) pencil_post_seg_kernel(PArgs<T> a, SegTabs st) {
+template <typename T, int S, int CB, int MINB>
+__global__ void __launch_bounds__(CB * 32, MINB) pencil_post_seg_kernel(PArgs<T> a, SegTabs st) {
   typedef typename Vec2<T>::type T2;
   extern __shared__ double sm_seg[];
   Mode md; Wave<T> wv; Ctx c;
@@ -462,7 +462,9 @@ static int seg_len(int ny) { return ny <= 256 ? 8 : (ny <= 512 ? 16 : (ny <= 768
 int seg_supported(chan_handle* h) { return seg_len(h->d.ny) != 0 && h->d.ny >= 16; }
 
 int seg_setup(chan_handle* h) {
-  const int ny = h->d.ny, S = seg_len(ny);
+  const int ny = h->d.ny;
+  int S = seg_len(ny);
+  if (h->tune.seg_shape > 0) S = h->tune.seg_shape / 100;          // experiment knob: S*100 + CB
   h->seg_S = S;
   // prefix products of the folded d/dy LU (direction 0) inside each segment
   std::vector<double> tab(21 * (size_t)ny), pf(ny), pb(ny);
@@ -482,7 +484,7 @@ int seg_setup(chan_handle* h) {
   return CHAN_OK;
 }
 
-template <typename T, int S, int CB>
+template <typename T, int S, int CB, int MINB = 1>
 static int launch_seg(chan_handle* h, bool post, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   static const float kAlpha[3] = { 29.0f / 96.0f, -3.0f / 40.0f, 1.0f / 6.0f }, kDseda[3] = { 0.0f, -17.0f / 60.0f, -5.0f / 12.0f };
@@ -497,10 +499,10 @@ static int launch_seg(chan_handle* h, bool post, int n) {
     unsigned pg = (unsigned)((h->d.M + 127) / 128);
     if (!h->pivH_ready) { pivot_kernel<T><<<pg, 128, 0, h->stream>>>(a, h->pivH, 0); h->launches++; h->pivH_ready = 1; }
     pivot_kernel<T><<<pg, 128, 0, h->stream>>>(a, h->pivI, 1); h->launches++;
-    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_post_seg_kernel<T, S, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    pencil_post_seg_kernel<T, S, CB><<<grid, block, sm, h->stream>>>(a, st);
+    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_post_seg_kernel<T, S, CB, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    pencil_post_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st);
   } else {
-    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     PeerOut po; memset(&po, 0, sizeof(po));
     po.nranks = h->peer_ready ? h->cfg.size : 1;
     if (h->peer_ready) {
@@ -510,7 +512,7 @@ static int launch_seg(chan_handle* h, bool post, int n) {
         for (int f = 0; f < 6; f++) po.rcv[p][f] = h->peer_rcv[p][f];
       }
     }
-    pencil_pre_seg_kernel<T, S, CB><<<grid, block, sm, h->stream>>>(a, st, po);
+    pencil_pre_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st, po);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
@@ -518,6 +520,17 @@ static int launch_seg(chan_handle* h, bool post, int n) {
 }
 template <typename T>
 static int launch_seg_any(chan_handle* h, bool post, int n) {
+  if (h->tune.seg_shape > 0) {
+    switch (h->tune.seg_shape) {
+      case 408: return launch_seg<T, 4, 8, 2>(h, post, n);
+      case 409: return launch_seg<T, 4, 8, 3>(h, post, n);
+      case 416: return launch_seg<T, 4, 16, 1>(h, post, n);
+      case 808: return launch_seg<T, 8, 8, 2>(h, post, n);
+      case 809: return launch_seg<T, 8, 8, 3>(h, post, n);
+      case 804: return launch_seg<T, 8, 4, 4>(h, post, n);
+      default: break;
+    }
+  }
   switch (h->seg_S) {
     case 8: return launch_seg<T, 8, 16>(h, post, n);
     case 16: return launch_seg<T, 16, 16>(h, post, n);

@@ -22,6 +22,9 @@
 //    Q[f][plane][x][kz] is produced and consumed per plane batch sized to stay
 //    resident in the 126 MB L2.
 #include "plane_core.cuh"
+#ifndef ZMINB
+#define ZMINB 2
+#endif
 
 namespace chan {
 using namespace fft;
@@ -51,10 +54,10 @@ __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* src = a.src[f];
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
   __syncthreads();
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.px.radix[t], a.px.span[t], TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
 }
 
 // x forward: natural-order x line -> truncated compact spectral rows
@@ -67,10 +70,10 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   if (a.dbg_skip & 2) return;
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
-  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, t, TK, TK, TK, TK, tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
+  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, a.px.radix[t], a.px.span[t], TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
 // -------------------------------------------------------------------------------
@@ -90,7 +93,7 @@ __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double 
 }
 
 template <typename T, int MODE>
-__global__ void __launch_bounds__(256, 2) zstage_kernel(ZArgs<T> a) {
+__global__ void __launch_bounds__(256, ZMINB) zstage_kernel(ZArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
@@ -104,18 +107,18 @@ __global__ void __launch_bounds__(256, 2) zstage_kernel(ZArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.pz);
   const size_t fstride = (size_t)a.pb * a.nx * a.Kz;
   T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
-  FFT_DISPATCH_RADIX(pl.radix[0], (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
   if (a.dbg_stop == 1) return;
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, t, a.SS, ST, ST, ST, tid, nthr); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], a.pz.span[t], a.SS, ST, ST, ST, tid, nthr, pl.r_first); __syncthreads(); }
   if (a.dbg_stop == 2) return;
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
   if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
-  switch (pl.radix[pl.nstage - 1]) {
-    case 2: z_mid_fused<T2, 2, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    case 3: z_mid_fused<T2, 3, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    default: z_mid_fused<T2, 4, MODE>(s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+  switch (pl.r_last) {
+    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
   if (MODE == ZM_EXPORT) return;
   if (a.dbg_stop == 3) return;
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(256, 2) zstage_kernel(ZArgs<T> a) {
     double v = 0; for (int wi = 0; wi < (nthr >> 5); wi++) v = fmax(v, red[tid][wi]);
     atomic_max_pos(a.umax_bits + tid, v);
   }
-  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, t, a.SS, a.XP * NOUT, NOUT, NIN, tid, nthr); __syncthreads(); }
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], a.pz.span[t], a.SS, a.XP * NOUT, NOUT, NOUT, tid, nthr, pl.r_first); __syncthreads(); }
   if (a.dbg_stop == 4) return;
   z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr);
 }
@@ -183,7 +186,7 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   // an odd number of elements per position keeps the register-fused middle stage (threads stride
   // over positions) free of bank conflicts
   int ss = xp * nin; if (h->tune.z_pad && !(ss & 1)) ss++;
-  size_t sm = (size_t)n * ss * sizeof(T2);
+  size_t sm = ((size_t)n * ss + n / h->pz.radix[0]) * sizeof(T2);      // rows + their skew (plane_core.cuh)
   if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
   a.XP = xp; a.SS = ss;
   CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

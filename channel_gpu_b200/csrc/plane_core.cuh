@@ -19,11 +19,12 @@
 namespace chan {
 namespace fft {
 
-template <class T2> struct PlanT { int n, nstage; int radix[16], span[16]; const T2* tw; const int* inv; const int* pos; };
+// scalar view of an FftPlan: the radix/span arrays are read from the FftPlan itself (a kernel parameter,
+// i.e. constant bank) so that no per-thread local copy of them is made
+template <class T2> struct PlanT { int n, nstage, r_first, r_last; const T2* tw; const int* inv; const int* pos; };
 
 template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
-  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage;
-  for (int i = 0; i < 16; i++) { q.radix[i] = p.radix[i]; q.span[i] = p.span[i]; }
+  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage; q.r_first = p.radix[0]; q.r_last = p.radix[p.nstage - 1];
   q.tw = (const T2*)p.tw; q.inv = p.inv; q.pos = p.pos;
   return q;
 }
@@ -54,8 +55,10 @@ FFT_HD void x_inv_load_stage0(T2* s, const T2* src, const SegMap& sm, int jl, co
     // all R loads are issued back to back (clamped address + select), never behind a branch
     T2 a[R]; int ik[R];
 #pragma unroll
+    const int nq0 = FFT_LDG(pl.inv + g * R);       // inv[g*R + q] = inv[g*R] + q*(n/R)  (perm_pos, kernels_tables.cu)
+#pragma unroll
     for (int q = 0; q < R; q++) {
-      int nq = FFT_LDG(pl.inv + g * R + q);
+      int nq = nq0 + q * ng;
       ik[q] = nq <= kxmax ? nq : (nq >= n - kxmax ? nq - n + Kx : -1);
     }
     const bool kz_ok = kz < Kz;
@@ -112,9 +115,10 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
     for (int i = 0; i < R; i++) a[i] = s[(size_t)(g * R + i) * TK + t];
     Dft<R, -1, T2>::run(a);
     if (kz < Kz) {
+      const int np0 = FFT_LDG(pl.inv + g * R);
 #pragma unroll
       for (int p = 0; p < R; p++) {
-        int np = FFT_LDG(pl.inv + g * R + p);
+        int np = np0 + p * ng;
         int ikx = np <= kxmax ? np : (np >= n - kxmax ? np - n + Kx : -1);
         if (ikx >= 0) {
           T2 v = a[p];
@@ -128,14 +132,21 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
 template <class T2, int SIGN, bool DIT>
-FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int t, int st, int nlines, int nact, int nper, int tid, int nthr) {
-  int r = pl.radix[t], m = pl.span[t];
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, m, st, nlines, nact, nper, pl.tw, tid, nthr)));
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, int m, int st, int nlines, int nact, int nper, int tid, int nthr, int sk = 0) {
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, m, st, nlines, nact, nper, pl.tw, tid, nthr, sk)));
 }
 
 // =================================== z direction =================================================
-// One block works on XP x-pairs; shared layout s[pos*ST + xpl*NIN + f], ST = XP*NIN.
+// One block works on XP x-pairs; shared layout s[zrow(pos) + slot], zrow(pos) = pos*SS + pos/r_0 (SS odd,
+// >= XP*NIN; the pos/r_0 skew is explained at z_unpack_store).  Inverse side: slot = xpl*NIN + f.  Forward
+// side: slot = xpl*NOUT + f, i.e. the NOUT output lines of all x-pairs are packed next to each other so
+// that the forward stages touch contiguous elements (z_mid_fused makes the switch behind a barrier).
 // Two-for-one: line (xpl, f) holds field f at x0 = 2*xp (real part) and x1 = 2*xp+1 (imaginary part).
+#ifdef __CUDA_ARCH__
+#define FFT_BLOCK_SYNC() __syncthreads()
+#else
+#define FFT_BLOCK_SYNC()
+#endif
 
 // value of the Hermitian-extended, zero-padded packed spectrum at natural index nz
 // index and kind of the Hermitian-extended, zero-padded packed spectrum at natural index nz:
@@ -165,11 +176,12 @@ FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T
       const T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
       // loads are issued in independent batches of <= 8 pairs (clamped address + select), never behind a branch
       constexpr int HB = R == 16 ? 8 : (R == 12 ? 6 : R);
+      const int nz0 = FFT_LDG(pl.inv + g * R);     // inv[g*R + q] = inv[g*R] + q*(n/R)
 #pragma unroll
       for (int h0 = 0; h0 < R; h0 += HB) {
         int kk[HB], kind[HB]; T2 B[HB];
 #pragma unroll
-        for (int i = 0; i < HB; i++) z_packed_index(FFT_LDG(pl.inv + g * R + h0 + i), n, Kz, kk[i], kind[i]);
+        for (int i = 0; i < HB; i++) z_packed_index(nz0 + (h0 + i) * ng, n, Kz, kk[i], kind[i]);
 #pragma unroll
         for (int i = 0; i < HB; i++) { a[h0 + i] = qa[kk[i]]; B[i] = qa[Kz + kk[i]]; }
 #pragma unroll
@@ -181,7 +193,7 @@ FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T
       for (int i = 0; i < R; i++) a[i] = mk2<T2>(0, 0);
     }
 #pragma unroll
-    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * SS + li] = a[p];
+    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * SS + g + li] = a[p];     // skew(g*R + p) = g
   }
 }
 
@@ -189,67 +201,92 @@ enum { ZM_ROTOR = 0, ZM_IDENTITY = 1, ZM_EXPORT = 2 };
 
 // last inverse stage + pointwise + first forward stage, all 'NIN' lines of one x-pair in registers.
 // umax3: per-thread running maxima of |u|,|v|,|w| (ROTOR).  phys0/phys1: output rows (EXPORT).
+// Reads the inverse-side slots of s_in, writes the forward-side slots of s_out.  On the device
+// s_out == s_in: the packed output slots of x-pair xpl overlap input slots of x-pairs <= xpl, which are
+// read in the same or an earlier round of the loop, so one barrier per round between the reads and the
+// writes is enough.  The host emulation (threads run one after the other) passes a separate s_out.
 template <class T2, int R, int MODE>
-FFT_HD void z_mid_fused(T2* s, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
+FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
                         typename RealOf<T2>::type* umax3, typename RealOf<T2>::type* phys, size_t phys_xstride, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
-  const int n = pl.n, m = n / R;
-  for (int b = tid; b < m * XP; b += nthr) {
-    int k = b % m, xpl = b / m;
-    if (xpl >= nxp_valid) continue;
+  const int n = pl.n, m = n / R, sk = pl.r_first;
+  const int ist = m * SS + m / sk;                       // r_0 divides m = n / r_last (nstage >= 2)
+  const T rn2 = ((T)1 / n2) * ((T)1 / n2);
+  const int nround = (m * XP + nthr - 1) / nthr;
+  for (int it = 0; it < nround; it++) {
+    const int b = tid + it * nthr;
+    const int k = b % m, xpl = b / m;
+    const bool work = b < m * XP && xpl < nxp_valid;
+    const size_t row = (size_t)k * SS + k / sk;
     T2 a[NIN][R];
+    if (work) {
 #pragma unroll
-    for (int f = 0; f < NIN; f++) {
+      for (int f = 0; f < NIN; f++) {
 #pragma unroll
-      for (int i = 0; i < R; i++) a[f][i] = s[(size_t)(k + i * m) * SS + xpl * NIN + f];
-      apply_twiddles<R, +1, T2>(a[f], pl.tw, k, 1);
-      Dft<R, +1, T2>::run(a[f]);
-    }
-    if (MODE == ZM_EXPORT) {
-      T* o0 = phys + (size_t)(2 * xpl) * phys_xstride; T* o1 = o0 + phys_xstride;
+        for (int i = 0; i < R; i++) a[f][i] = s_in[row + (size_t)i * ist + xpl * NIN + f];
+        apply_twiddles<R, +1, T2>(a[f], pl.tw, k, 1);
+        Dft<R, +1, T2>::run(a[f]);
+      }
+      if (MODE == ZM_EXPORT) {
+        T* o0 = phys + (size_t)(2 * xpl) * phys_xstride; T* o1 = o0 + phys_xstride;
 #pragma unroll
-      for (int p = 0; p < R; p++) { o0[k + p * m] = a[0][p].x; o1[k + p * m] = a[0][p].y; }
-      continue;
-    }
-    if (MODE == ZM_ROTOR) {
-      // rotorkernel (convolution_kernels.cu:107-131): every factor divided by N2, m = u x omega;
-      // .x is the point (x0, z), .y the point (x1, z).  Maxima are of the un-normalised velocities.
+        for (int p = 0; p < R; p++) { o0[k + p * m] = a[0][p].x; o1[k + p * m] = a[0][p].y; }
+      }
+      if (MODE == ZM_ROTOR) {
+        // rotorkernel (convolution_kernels.cu:107-131): every factor divided by N2, m = u x omega;
+        // .x is the point (x0, z), .y the point (x1, z).  Maxima are of the un-normalised velocities.
 #pragma unroll
-      for (int p = 0; p < R; p++) {
-        T2 u = a[0][p], v = a[1][p], w = a[2][p], ox = a[3][p], oy = a[4][p], oz = a[5][p];
-        umax3[0] = fmax(umax3[0], fmax(fabs(u.x), fabs(u.y)));
-        umax3[1] = fmax(umax3[1], fmax(fabs(v.x), fabs(v.y)));
-        umax3[2] = fmax(umax3[2], fmax(fabs(w.x), fabs(w.y)));
-        u.x /= n2; v.x /= n2; w.x /= n2; u.y /= n2; v.y /= n2; w.y /= n2;
-        ox.x /= n2; oy.x /= n2; oz.x /= n2; ox.y /= n2; oy.y /= n2; oz.y /= n2;
-        a[0][p] = mk2<T2>(v.x * oz.x - w.x * oy.x, v.y * oz.y - w.y * oy.y);
-        a[1][p] = mk2<T2>(w.x * ox.x - u.x * oz.x, w.y * ox.y - u.y * oz.y);
-        a[2][p] = mk2<T2>(u.x * oy.x - v.x * ox.x, u.y * oy.y - v.y * ox.y);
+        for (int p = 0; p < R; p++) {
+          T2 u = a[0][p], v = a[1][p], w = a[2][p], ox = a[3][p], oy = a[4][p], oz = a[5][p];
+          umax3[0] = fmax(umax3[0], fmax(fabs(u.x), fabs(u.y)));
+          umax3[1] = fmax(umax3[1], fmax(fabs(v.x), fabs(v.y)));
+          umax3[2] = fmax(umax3[2], fmax(fabs(w.x), fabs(w.y)));
+          // (v/N2)(oz/N2) - (w/N2)(oy/N2) as one scaling by 1/N2^2: 12 divisions per point were 15 % of the
+          // kernel's instructions; the result differs from the divide-first form in the last bit only
+          a[0][p] = mk2<T2>((v.x * oz.x - w.x * oy.x) * rn2, (v.y * oz.y - w.y * oy.y) * rn2);
+          a[1][p] = mk2<T2>((w.x * ox.x - u.x * oz.x) * rn2, (w.y * ox.y - u.y * oz.y) * rn2);
+          a[2][p] = mk2<T2>((u.x * oy.x - v.x * ox.x) * rn2, (u.y * oy.y - v.y * ox.y) * rn2);
+        }
+      }
+      if (MODE != ZM_EXPORT) {
+#pragma unroll
+        for (int f = 0; f < NOUT; f++) {
+          Dft<R, -1, T2>::run(a[f]);
+          apply_twiddles<R, -1, T2>(a[f], pl.tw, k, 1);
+        }
       }
     }
+    if (MODE == ZM_EXPORT) continue;
+    if (NOUT != NIN) FFT_BLOCK_SYNC();
+    if (work) {
 #pragma unroll
-    for (int f = 0; f < NOUT; f++) {
-      Dft<R, -1, T2>::run(a[f]);
-      apply_twiddles<R, -1, T2>(a[f], pl.tw, k, 1);
+      for (int f = 0; f < NOUT; f++) {
 #pragma unroll
-      for (int i = 0; i < R; i++) s[(size_t)(k + i * m) * SS + xpl * NIN + f] = a[f][i];
+        for (int i = 0; i < R; i++) s_out[row + (size_t)i * ist + xpl * NOUT + f] = a[f][i];
+      }
     }
   }
 }
 
 // Hermitian unpacking of the two-for-one pair + truncation to kz < Kz, from the digit-reversed
 // output of the forward transform
+// Threads run along k for coalesced stores, and consecutive k are digit-reversed positions that
+// differ in their HIGH digits, i.e. rows a multiple of r_0 apart: with a plain row pitch they would
+// all fall into the same banks (7x the ideal number of wavefronts in the ncu source view).  The
+// pos/r_0 skew of the layout spreads exactly those rows over the banks.
 template <class T2, int NIN, int NOUT>
 FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
-  const int n = pl.n;
+  const int n = pl.n, sk = pl.r_first;
+  const float rsk = 1.0f / (float)sk;
   for (int b = tid; b < Kz * NOUT * XP; b += nthr) {
     int k = b % Kz, l = b / Kz, f = l % NOUT, xpl = l / NOUT;
     if (xpl >= nxp_valid) continue;
-    T2 Yk = s[(size_t)pl.pos[k] * SS + xpl * NIN + f];
-    T2 Yn = s[(size_t)pl.pos[k ? n - k : 0] * SS + xpl * NIN + f];
+    const int pk = FFT_LDG(pl.pos + k), pn = FFT_LDG(pl.pos + (k ? n - k : 0));
+    T2 Yk = s[(size_t)pk * SS + skew_of(pk, sk, rsk) + xpl * NOUT + f];
+    T2 Yn = s[(size_t)pn * SS + skew_of(pn, sk, rsk) + xpl * NOUT + f];
     const T h = (T)0.5;
     T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
     qa[k] = mk2<T2>(h * (Yk.x + Yn.x), h * (Yk.y - Yn.y));

@@ -42,9 +42,9 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   for (auto& v : src) { v.x = (T)frand(); v.y = (T)frand(); }
   double err = 0, nrm = 0;
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
-    for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, t, TK, TK, TK, TK, tid, NTHR);
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
+    for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], H.p.span[t], TK, TK, TK, TK, tid, NTHR);
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
   }
   for (int kz = 0; kz < Kz; kz++) for (int x = 0; x < nx; x++) {
     cd acc = 0;
@@ -56,14 +56,14 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   // forward of the physical lines must give back nx * src on the active modes
   SegDst<T2> dsts; for (int i = 0; i < 8; i++) dsts.p[i] = dst.data();
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[pl.nstage - 1], (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
-    for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, t, TK, TK, TK, TK, tid, NTHR);
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
+    for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, H.p.radix[t], H.p.span[t], TK, TK, TK, TK, tid, NTHR);
+    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
   }
   err = nrm = 0;
   for (int i = 0; i < Kx; i++) for (int kz = 0; kz < Kz; kz++) { size_t o = at(i, kz); err += std::norm(cd(dst[o].x - src[o].x, dst[o].y - src[o].y)); nrm += std::norm(cd(src[o].x, src[o].y)); }
   double e2 = sqrt(err / nrm);
-  printf("  x n=%4d plan", nx); for (int i = 0; i < pl.nstage; i++) printf(" %d", pl.radix[i]);
+  printf("  x n=%4d plan", nx); for (int i = 0; i < pl.nstage; i++) printf(" %d", H.p.radix[i]);
   printf("  inv err %.2e  roundtrip err %.2e\n", e1, e2);
   return e1 > e2 ? e1 : e2;
 }
@@ -91,24 +91,24 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   PlanT<T2> pl = plan_of<T2>(H.p);
   int Kz = n / 3 + 1, nxrows = 2 * XP, ST = XP * NIN, SS = ST | 1;
   size_t fstride = (size_t)nxrows * Kz;
-  std::vector<T2> Q((size_t)NIN * fstride), Q0, s((size_t)n * SS);
+  std::vector<T2> Q((size_t)NIN * fstride), Q0, s((size_t)n * SS + n), s2((size_t)n * SS + n);
   for (auto& v : Q) { v.x = (T)frand(); v.y = (T)frand(); }
   Q0 = Q;
   T n2 = (T)7.0;
   std::vector<T> phys((size_t)nxrows * (n + 2), (T)0);
   T um[3] = { 0, 0, 0 };
-  EACH_THREAD { FFT_DISPATCH_RADIX(pl.radix[0], (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR))); }
-  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, t, SS, ST, ST, ST, tid, NTHR);
+  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR))); }
+  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], H.p.span[t], SS, ST, ST, ST, tid, NTHR, pl.r_first);
   EACH_THREAD {
-    switch (pl.radix[pl.nstage - 1]) {
-      case 2: z_mid_fused<T2, 2, MODE>(s.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      case 3: z_mid_fused<T2, 3, MODE>(s.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      default: z_mid_fused<T2, 4, MODE>(s.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+    switch (pl.r_last) {
+      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
     }
   }
   if (MODE != ZM_EXPORT) {
-    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, t, SS, XP * NOUT, NOUT, NIN, tid, NTHR);
-    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR);
+    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], H.p.span[t], SS, XP * NOUT, NOUT, NOUT, tid, NTHR, pl.r_first);
+    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR);
   }
   // reference
   double err = 0, nrm = 0, umref[3] = { 0, 0, 0 };
@@ -141,7 +141,7 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   // rows of invalid pairs must be untouched
   for (int f = 0; f < NOUT; f++) for (int xr = 2 * nxp_valid; xr < nxrows; xr++) for (int k = 0; k < Kz; k++)
     if (Q[f * fstride + (size_t)xr * Kz + k].x != Q0[f * fstride + (size_t)xr * Kz + k].x) e = 1.0;
-  printf("  z n=%4d mode %d XP=%d/%d plan", n, MODE, nxp_valid, XP); for (int i = 0; i < pl.nstage; i++) printf(" %d", pl.radix[i]);
+  printf("  z n=%4d mode %d XP=%d/%d plan", n, MODE, nxp_valid, XP); for (int i = 0; i < pl.nstage; i++) printf(" %d", H.p.radix[i]);
   printf("  err %.2e\n", e);
   return e;
 }
