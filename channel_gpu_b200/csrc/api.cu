@@ -73,7 +73,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
       { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 256 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 } };
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 } };
     for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
   }
   Dims& d = h->d;
@@ -105,7 +105,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   const size_t fb = field_bytes(h);
   void** fields[11] = { &h->phi, &h->g, &h->v, &h->dv, &h->Rphi, &h->Rg, &h->u, &h->w, &h->ox, &h->oy, &h->oz };
   for (int i = 0; i < 11; i++) if ((rc = alloc_dev(h, fields[i], fb))) return rc;
-  const size_t chain = (size_t)d.ny * 2 * d.M * sizeof(double);
+  const size_t chain = (size_t)d.ny * ((2 * d.M + 31) / 32 * 32) * sizeof(double);   // whole warp tiles (pencil_post scratch layout)
   if ((rc = alloc_dev(h, (void**)&h->sA, chain))) return rc;
   if ((rc = alloc_dev(h, (void**)&h->sB, chain))) return rc;
   if ((rc = alloc_dev(h, (void**)&h->sC, chain))) return rc;

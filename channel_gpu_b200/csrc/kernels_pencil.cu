@@ -219,6 +219,32 @@ __device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, 
 }
 
 // phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
+#ifndef PU1
+#define PU1 6
+#define PU2 8
+#define PU3 3
+#define PU4 8
+#define PU5 8
+#define PU6 8
+#define PU7 8
+#endif
+// Sweep driver of pencil_post.  A thread's rows are strictly sequential, and the hardware issues in
+// order, so with "load row j+1, then work on row j" only ONE row of loads is in flight per thread and a
+// pass costs one memory latency per row (the ablation in profiles/r01_post_passes.txt: the passes with
+// few bytes per row ran at 2-4 TB/s).  Here the loads of U rows are issued back to back, then the U
+// dependent row updates follow.  ld(jj) returns the loaded row jj of the sweep, pr(jj, row) works on it.
+template <int U, class Load, class Proc>
+__device__ __forceinline__ void sweep_rows(int ny, Load ld, Proc pr) {
+  for (int j0 = 0; j0 < ny; j0 += U) {
+    decltype(ld(0)) r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) r[u] = ld(min(j0 + u, ny - 1));        // clamped: a harmless reload
+    __syncwarp();          // both lanes of a mode hold their rows before either overwrites shared pivots
+#pragma unroll
+    for (int u = 0; u < U; u++) if (j0 + u < ny) pr(j0 + u, r[u]);
+  }
+}
+
 template <typename T>
 __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
                            T* phi, T* v, T* dv, double dvm, double dvp) {
@@ -231,21 +257,19 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   double det = q.dv1 * p.dv2 - p.dv1 * q.dv2;
   double c1 = p.dv2 * dvm - q.dv2 * dvp; c1 = -c1 / det;
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
-  T* pp = phi + md.e; T* pv = v + md.e; T* pd = dv + md.e;
-  const double* yt = a.yt.y;
-  T pc = *pp, vc = *pv, dc = *pd;
-  for (int j = 0; j < ny; j++) {
-    T pn = pc, vn = vc, dn = dc;
-    if (j + 1 < ny) { pn = pp[st]; vn = pv[st]; dn = pd[st]; }
-    BcFun f = bc_functions(k, __ldg(yt), md.c);
-    double ppv = (double)pc, vv = (double)vc, dd = (double)dc;
-    ppv = ppv + c1 * f.ddv1 + c2 * f.ddv2;
-    dd = dd + c1 * f.dv1 + c2 * f.dv2;
-    vv = vv + c1 * f.v1 + c2 * f.v2;
-    if (md.zero_mode) { ppv = 0.0; vv = 0.0; dd = 0.0; }
-    *pp = (T)ppv; *pv = (T)vv; *pd = (T)dd;
-    pc = pn; vc = vn; dc = dn; pp += st; pv += st; pd += st; yt++;
-  }
+  T* const pp = phi + md.e; T* const pv = v + md.e; T* const pd = dv + md.e;
+  struct Row { T p, v, d; };
+  sweep_rows<PU7>(ny,
+    [&](int j) { Row r; r.p = pp[(long)j * st]; r.v = pv[(long)j * st]; r.d = pd[(long)j * st]; return r; },
+    [&](int j, const Row& r) {
+      BcFun f = bc_functions(k, __ldg(a.yt.y + j), md.c);
+      double ppv = (double)r.p, vv = (double)r.v, dd = (double)r.d;
+      ppv = ppv + c1 * f.ddv1 + c2 * f.ddv2;
+      dd = dd + c1 * f.dv1 + c2 * f.dv2;
+      vv = vv + c1 * f.v1 + c2 * f.v2;
+      if (md.zero_mode) { ppv = 0.0; vv = 0.0; dd = 0.0; }
+      pp[(long)j * st] = (T)ppv; pv[(long)j * st] = (T)vv; pd[(long)j * st] = (T)dd;
+    });
 }
 
 // =================================================================================
@@ -333,149 +357,138 @@ __global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
 // pencil_post: H1..3, phi, g, R_phi, R_g -> phi, g, v, dv, R_phi, R_g   (7 passes)
 // =================================================================================
 template <typename T>
-__global__ void __launch_bounds__(128) pencil_post_kernel(PArgs<T> a) {
+__global__ void __launch_bounds__(128, 4) pencil_post_kernel(PArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   Mode md; Wave<T> wv;
   if (!setup(a, md, wv)) return;
   const long st = 2 * a.M, M = a.M; const int ny = a.ny; const int c = md.c; const long e = md.e;
   const T dt = (T)a.sc->dt;
   const T s = wv.sc;
-  const long top = (long)(ny - 1);
-  // Every pass walks its arrays with running pointers (rows are `st` reals / `M` complex apart) and keeps
-  // two rows in flight: the loads of the next row are issued before the current row is computed.
+  const int top = ny - 1;
+  // The scratch belongs to this kernel alone, so it is tiled per warp: [32 chains][row][lane] (pivots:
+  // [16 modes][row][lane pair]).  A warp then streams through ONE contiguous piece of memory per scratch
+  // array instead of touching a 256-byte fragment of every 2M-wide row.
+  const int sst = 32, pst = 16;
+  double* const sA0 = a.sA + (e >> 5) * 32 * ny + (e & 31);
+  double* const sB0 = a.sB + (e >> 5) * 32 * ny + (e & 31);
+  double* const sC0 = a.sC + (e >> 5) * 32 * ny + (e & 31);
+  double* const sP0 = a.sP + (md.m >> 4) * 16 * ny + (md.m & 15);
+  const T2* const H1 = a.ox + md.m; const T2* const H3 = a.oz + md.m; const T* const H2 = (const T*)a.oy + e;
+  T* const phi = (T*)a.phi + e; T* const g = (T*)a.g + e;
   // P1 (up): eliminate d/dy of phi, g and hv = -i (k1 H1 + k3 H3)  (calcHvgkernel, nonLinear_kernels.cu:129-130)
   {
     ElimD1P ep, eg, eh;
-    const T2* pH1 = a.ox + md.m; const T2* pH3 = a.oz + md.m;
-    const T* pp = (const T*)a.phi + e; const T* pg = (const T*)a.g + e;
-    double* sa = a.sA + e; double* sb = a.sB + e; double* sc = a.sC + e;
-    T2 h1 = *pH1, h3 = *pH3; T p = *pp, g = *pg;
-    for (int j = 0; j < ny; j++) {
-      T2 h1n = h1, h3n = h3; T pn = p, gn = g;
-      if (j + 1 < ny) { h1n = pH1[M]; h3n = pH3[M]; pn = pp[st]; gn = pg[st]; }
-      T h1p = other<T2, T>(h1, c), h3p = other<T2, T>(h3, c);
-      T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
-      ep.step(a.yt.d1[0], j, ny, (double)p, sa, st);
-      eg.step(a.yt.d1[0], j, ny, (double)g, sb, st);
-      eh.step(a.yt.d1[0], j, ny, (double)hv, sc, st);
-      h1 = h1n; h3 = h3n; p = pn; g = gn;
-      pH1 += M; pH3 += M; pp += st; pg += st; sa += st; sb += st; sc += st;
-    }
+    struct Row { T2 h1, h3; T p, g; };
+    sweep_rows<PU1>(ny,
+      [&](int j) { Row r; r.h1 = H1[(long)j * M]; r.h3 = H3[(long)j * M]; r.p = phi[(long)j * st]; r.g = g[(long)j * st]; return r; },
+      [&](int j, const Row& r) {
+        T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
+        T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
+        ep.step(a.yt.d1[0], j, ny, (double)r.p, sA0 + j * sst, sst);
+        eg.step(a.yt.d1[0], j, ny, (double)r.g, sB0 + j * sst, sst);
+        eh.step(a.yt.d1[0], j, ny, (double)hv, sC0 + j * sst, sst);
+      });
   }
+  if (a.dbg_stop == 1) return;
   // P2 (down): phi', g', hv' ; eliminate d/dy of phi', g' (second derivative = d/dy twice, Q4)
   {
     ElimD1P ep, eg;
     double xp = 0.0, xg = 0.0, xh = 0.0;
-    double* sa = a.sA + top * st + e; double* sb = a.sB + top * st + e; double* sc = a.sC + top * st + e;
-    const double* cpt = a.yt.d1[0].cp + top;
-    double dA = *sa, dB = *sb, dC = *sc;
-    for (int jj = 0; jj < ny; jj++) {
-      double dAn = dA, dBn = dB, dCn = dC;
-      if (jj + 1 < ny) { dAn = sa[-st]; dBn = sb[-st]; dCn = sc[-st]; }
-      double cp = __ldg(cpt);
-      xp = dA - cp * xp; xg = dB - cp * xg; xh = dC - cp * xh;
-      *sc = rnd<T>(xh);
-      ep.step(a.yt.d1[1], jj, ny, rnd<T>(xp), sa, -st);
-      eg.step(a.yt.d1[1], jj, ny, rnd<T>(xg), sb, -st);
-      dA = dAn; dB = dBn; dC = dCn;
-      sa -= st; sb -= st; sc -= st; cpt--;
-    }
+    struct Row { double dA, dB, dC; };
+    sweep_rows<PU2>(ny,
+      [&](int jj) { int j = top - jj; Row r; r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.dC = sC0[j * sst]; return r; },
+      [&](int jj, const Row& r) {
+        const int j = top - jj;
+        double cp = __ldg(a.yt.d1[0].cp + j);
+        xp = r.dA - cp * xp; xg = r.dB - cp * xg; xh = r.dC - cp * xh;
+        sC0[j * sst] = rnd<T>(xh);
+        ep.step(a.yt.d1[1], jj, ny, rnd<T>(xp), sA0 + j * sst, -sst);
+        eg.step(a.yt.d1[1], jj, ny, rnd<T>(xg), sB0 + j * sst, -sst);
+      });
   }
+  if (a.dbg_stop == 2) return;
   // P3 (up): phi'', g'' -> explicit RK update (rk_step_1/2, RK3_kernels.cu:76-80,138-142) -> eliminate implicit solves
   const double bdt = (double)(dt * a.betha);                         // dt*betha in the state type (:235)
   const double Dimp = a.nuD * bdt;
   {
     ElimVarP<2> ev;
     double xp = 0.0, xg = 0.0;
-    double* sa = a.sA + e; double* sb = a.sB + e; const double* sc = a.sC + e; double* sp = a.sP + md.m;
-    const T2* pH1 = a.ox + md.m; const T2* pH3 = a.oz + md.m; const T* pH2 = (const T*)a.oy + e;
-    const T* pp = (const T*)a.phi + e; const T* pg = (const T*)a.g + e;
-    T* pRp = (T*)a.Rphi + e; T* pRg = (T*)a.Rg + e;
-    const double* cpt = a.yt.d1[1].cp + top;
+    T* const Rp = (T*)a.Rphi + e; T* const Rg = (T*)a.Rg + e;
     struct Row { double dA, dB, dC; T2 h1, h3; T h2, p, g, rp, rg; };
-    Row r;
-    r.dA = *sa; r.dB = *sb; r.dC = *sc; r.h1 = *pH1; r.h3 = *pH3; r.h2 = *pH2; r.p = *pp; r.g = *pg; r.rp = *pRp; r.rg = *pRg;
-    for (int j = 0; j < ny; j++) {
-      Row n = r;
-      if (j + 1 < ny) {
-        n.dA = sa[st]; n.dB = sb[st]; n.dC = sc[st]; n.h1 = pH1[M]; n.h3 = pH3[M];
-        n.h2 = pH2[st]; n.p = pp[st]; n.g = pg[st]; n.rp = pRp[st]; n.rg = pRg[st];
-      }
-      double cp = __ldg(cpt);
-      xp = r.dA - cp * xp; xg = r.dB - cp * xg;
-      T pyy = (T)xp, gyy = (T)xg;
-      T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
-      T rp_new = (T)r.dC - wv.kk * r.h2;                              // calcHvvkernel (:180-181)
-      T rg_new = s * (wv.k3 * h1p - wv.k1 * h3p);                     // h_g = i (k3 H1 - k1 H3) (:132-133)
-      T pw = r.p + dt * (a.alpha * a.nuT * (pyy - wv.kk * r.p) + a.dseda * r.rp);
-      T gw = r.g + dt * (a.alpha * a.nuT * (gyy - wv.kk * r.g) + a.dseda * r.rg);
-      pw = pw + dt * a.gammad * rp_new;
-      gw = gw + dt * a.gammad * rg_new;
-      *pRp = rp_new; *pRg = rg_new;
-      const double f[2] = { (double)pw, (double)gw };
-      double* const cur[2] = { sa, sb };
-      ev.step(a.yt.d2[0], j, ny, f, true, wv.kkd, Dimp, cur, st, sp, M);
-      r = n;
-      sa += st; sb += st; sc += st; sp += M; pH1 += M; pH3 += M; pH2 += st; pp += st; pg += st; pRp += st; pRg += st; cpt--;
-    }
+    sweep_rows<PU3>(ny,
+      [&](int j) {
+        Row r; r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.dC = sC0[j * sst]; r.h1 = H1[(long)j * M]; r.h3 = H3[(long)j * M];
+        r.h2 = H2[(long)j * st]; r.p = phi[(long)j * st]; r.g = g[(long)j * st]; r.rp = Rp[(long)j * st]; r.rg = Rg[(long)j * st];
+        return r;
+      },
+      [&](int j, const Row& r) {
+        double cp = __ldg(a.yt.d1[1].cp + (top - j));
+        xp = r.dA - cp * xp; xg = r.dB - cp * xg;
+        T pyy = (T)xp, gyy = (T)xg;
+        T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
+        T rp_new = (T)r.dC - wv.kk * r.h2;                              // calcHvvkernel (:180-181)
+        T rg_new = s * (wv.k3 * h1p - wv.k1 * h3p);                     // h_g = i (k3 H1 - k1 H3) (:132-133)
+        T pw = r.p + dt * (a.alpha * a.nuT * (pyy - wv.kk * r.p) + a.dseda * r.rp);
+        T gw = r.g + dt * (a.alpha * a.nuT * (gyy - wv.kk * r.g) + a.dseda * r.rg);
+        pw = pw + dt * a.gammad * rp_new;
+        gw = gw + dt * a.gammad * rg_new;
+        Rp[(long)j * st] = rp_new; Rg[(long)j * st] = rg_new;
+        const double f[2] = { (double)pw, (double)gw };
+        double* const cur[2] = { sA0 + j * sst, sB0 + j * sst };
+        ev.step(a.yt.d2[0], j, ny, f, true, wv.kkd, Dimp, cur, sst, sP0 + j * pst, pst);
+      });
   }
-  // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new
+  if (a.dbg_stop == 3) return;
+  // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new.  The Helmholtz elimination
+  // lags one row ABOVE the row being read, so the batch of rows below still holds the implicit-solve data.
   {
     ElimVarP<1> eh;
     double xp = 0.0, xg = 0.0;
-    double* sa = a.sA + top * st + e; const double* sb = a.sB + top * st + e; double* sp = a.sP + top * M + md.m;
-    T* pp = (T*)a.phi + top * st + e; T* pg = (T*)a.g + top * st + e;
-    double dA = *sa, dB = *sb, cp = *sp;
-    for (int jj = 0; jj < ny; jj++) {
-      double dAn = dA, dBn = dB, cpn = cp;
-      // rows below are still the implicit-solve data: the Helmholtz elimination lags one row ABOVE
-      if (jj + 1 < ny) { dAn = sa[-st]; dBn = sb[-st]; cpn = sp[-M]; }
-      xp = dA - cp * xp; xg = dB - cp * xg;
-      // both components of a mode share the pivot row: every lane must have read its pivots before
-      // any lane overwrites the row above with the Helmholtz pivot of the lagging row
-      __syncwarp();
-      *pg = (T)xg;
-      *pp = (T)xp;
-      const double f[1] = { rnd<T>(xp) };
-      double* const cur[1] = { sa };
-      eh.step(a.yt.d2[1], jj, ny, f, false, wv.kkd, 0.0, cur, -st, sp, -M);
-      dA = dAn; dB = dBn; cp = cpn;
-      sa -= st; sb -= st; sp -= M; pp -= st; pg -= st;
-    }
+    struct Row { double dA, dB, cp; };
+    sweep_rows<PU4>(ny,
+      [&](int jj) { int j = top - jj; Row r; r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.cp = sP0[j * pst]; return r; },
+      [&](int jj, const Row& r) {
+        const int j = top - jj;
+        xp = r.dA - r.cp * xp; xg = r.dB - r.cp * xg;
+        g[(long)j * st] = (T)xg;
+        phi[(long)j * st] = (T)xp;
+        const double f[1] = { rnd<T>(xp) };
+        double* const cur[1] = { sA0 + j * sst };
+        eh.step(a.yt.d2[1], jj, ny, f, false, wv.kkd, 0.0, cur, -sst, sP0 + j * pst, -pst);
+      });
   }
+  if (a.dbg_stop == 4) return;
   // P5 (up): v ; eliminate d/dy v
   {
     ElimD1P ev;
     double xv = 0.0;
-    double* sa = a.sA + e; const double* sp = a.sP + md.m; T* pv = (T*)a.v + e;
-    double dA = *sa, cp = *sp;
-    for (int j = 0; j < ny; j++) {
-      double dAn = dA, cpn = cp;
-      if (j + 1 < ny) { dAn = sa[st]; cpn = sp[M]; }
-      xv = dA - cp * xv;
-      *pv = (T)xv;
-      ev.step(a.yt.d1[0], j, ny, rnd<T>(xv), sa, st);
-      dA = dAn; cp = cpn;
-      sa += st; sp += M; pv += st;
-    }
+    T* const pv = (T*)a.v + e;
+    struct Row { double dA, cp; };
+    sweep_rows<PU5>(ny,
+      [&](int j) { Row r; r.dA = sA0[j * sst]; r.cp = sP0[j * pst]; return r; },
+      [&](int j, const Row& r) {
+        xv = r.dA - r.cp * xv;
+        pv[(long)j * st] = (T)xv;
+        ev.step(a.yt.d1[0], j, ny, rnd<T>(xv), sA0 + j * sst, sst);
+      });
   }
+  if (a.dbg_stop == 5) return;
   // P6 (down): dv
   double dvm = 0.0, dvp = 0.0;
   {
     double x = 0.0;
-    const double* sa = a.sA + top * st + e; T* pdv = (T*)a.dv + top * st + e;
-    const double* cpt = a.yt.d1[0].cp + top;
-    double dA = *sa;
-    for (int j = ny - 1; j >= 0; j--) {
-      double dAn = dA;
-      if (j > 0) dAn = sa[-st];
-      x = dA - __ldg(cpt) * x;
-      *pdv = (T)x;
-      if (j == ny - 1) dvp = rnd<T>(x);
-      if (j == 0) dvm = rnd<T>(x);
-      dA = dAn; sa -= st; pdv -= st; cpt--;
-    }
+    T* const pdv = (T*)a.dv + e;
+    sweep_rows<PU6>(ny,
+      [&](int jj) { return sA0[(top - jj) * sst]; },
+      [&](int jj, const double& dA) {
+        const int j = top - jj;
+        x = dA - __ldg(a.yt.d1[0].cp + j) * x;
+        pdv[(long)j * st] = (T)x;
+        if (j == top) dvp = rnd<T>(x);
+        if (j == 0) dvm = rnd<T>(x);
+      });
   }
+  if (a.dbg_stop == 6) return;
   // P7: wall correction (skipped when dt <= 1e-8, including the zeroing of mode (0,0))
   bc_correct<T>(a, md, wv, a.betha, dt, (T*)a.phi, (T*)a.v, (T*)a.dv, dvm, dvp);
 }
@@ -554,7 +567,7 @@ void fill_pencil_args(chan_handle* h, PArgs<T>& a) {
   a.nuD = 1.0 / (double)re;
   a.reD = (double)re;
   a.n = 0; a.alpha = a.dseda = a.gammad = a.betha = 0;
-  a.op = 0; a.f0 = a.f1 = a.f2 = 0; a.op_betha = 0; a.op_dt = 0; a.use_mean = 1;
+  a.op = 0; a.f0 = a.f1 = a.f2 = 0; a.op_betha = 0; a.op_dt = 0; a.use_mean = 1; a.pf_on = h->tune.post_pf; a.dbg_stop = h->tune.post_stop;
 }
 
 static const float kAlpha[3] = { 29.0f / 96.0f, -3.0f / 40.0f, 1.0f / 6.0f };     // RK3_kernels.cu:24
@@ -576,7 +589,8 @@ static int post_t(chan_handle* h, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
   long nchain = 2 * h->d.M;
-  pencil_post_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
+  const int bt = h->tune.post_threads;       // 64 or 128 (setup() derives the chain from blockIdx.x * blockDim.x)
+  pencil_post_kernel<T><<<(unsigned)((nchain + bt - 1) / bt), bt, 0, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;

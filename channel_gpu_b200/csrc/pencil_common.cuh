@@ -23,7 +23,7 @@ struct PArgs {
   int n;                   // RK substep
   T alpha, dseda, gammad, betha;
   // generic operator launches
-  int op; T2 *f0, *f1, *f2; T op_betha, op_dt; int use_mean;
+  int op; T2 *f0, *f1, *f2; T op_betha, op_dt; int use_mean; int pf_on, dbg_stop;
 };
 
 struct Mode {

@@ -169,8 +169,12 @@ FFT_HD T2 z_packed_combine(T2 A, T2 B, int k, int kind) {
 template <class T2, int R, int NIN>
 FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
   const int n = pl.n, ng = n / R, ST = XP * NIN;
+  // lanes run over the groups g: for a fixed input q the natural indices inv[g*R] + q*ng of the ng groups
+  // are a permutation of ng CONSECUTIVE kz, so a warp's load is one contiguous piece of a spectral row
+  // (lanes over the lines instead would touch one 32-byte sector per lane); the shared-memory stores are
+  // then R*SS + 1 elements apart, which the row skew makes conflict-free
   for (int b = tid; b < ng * ST; b += nthr) {
-    int li = b % ST, g = b / ST, f = li % NIN, xpl = li / NIN;
+    int g = b % ng, li = b / ng, f = li % NIN, xpl = li / NIN;
     T2 a[R];
     if (xpl < nxp_valid) {
       const T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
