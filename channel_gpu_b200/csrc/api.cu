@@ -138,7 +138,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // Measured on B200 (profiles/): the register version of `pre` always wins; `post` is instruction-
   // and latency-bound in both forms and the register version only pays when there are too few chains
   // to fill the GPU with one thread per chain (small grids, many GPUs).
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = 1 | ((2 * d.M < 148L * 64) ? 2 : 0);
+  // y stage: thread-per-chain kernels (batched row loads, HBM-bound) when there are enough chains to fill the
+  // SMs, the segment-parallel register kernels when a rank holds few chains (many ranks / small grids)
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = ((2 * d.M < 148L * 192) ? 1 : 0) | ((2 * d.M < 148L * 64) ? 2 : 0);
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
@@ -188,7 +190,7 @@ extern "C" int chan_ipc_import(chan_handle* h, int peer, const void* in) {
   if (have == h->cfg.size) {
     for (int f = 0; f < 6; f++) h->peer_rcv[h->cfg.rank][f] = h->rcv[f];
     h->peer_H[h->cfg.rank][0] = h->ox; h->peer_H[h->cfg.rank][1] = h->oy; h->peer_H[h->cfg.rank][2] = h->oz;
-    h->peer_ready = (h->tune.pencil_seg & 1) ? 1 : 0;      // the register `pre` kernel is the producer
+    h->peer_ready = 1;      // both `pre` kernels deliver their rows with peer stores
   }
   return CHAN_OK;
 }

@@ -30,6 +30,7 @@
 //                  here: truncated modes are not stored)
 // The state type T rounds exactly where the reference's cast_kernel does (after
 // every solve) and where its pointwise kernels compute in float.
+#include <string.h>
 #include "pencil_common.cuh"
 
 namespace chan {
@@ -188,6 +189,32 @@ struct ElimVarP {
 
 // ---- unfused building blocks (operator-level API, calcVdV) -------------------
 // out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
+#ifndef PU1
+#define PU1 6
+#define PU2 8
+#define PU3 3
+#define PU4 8
+#define PU5 8
+#define PU6 8
+#define PU7 8
+#endif
+// Sweep driver of pencil_post.  A thread's rows are strictly sequential, and the hardware issues in
+// order, so with "load row j+1, then work on row j" only ONE row of loads is in flight per thread and a
+// pass costs one memory latency per row (the ablation in profiles/r01_post_passes.txt: the passes with
+// few bytes per row ran at 2-4 TB/s).  Here the loads of U rows are issued back to back, then the U
+// dependent row updates follow.  ld(jj) returns the loaded row jj of the sweep, pr(jj, row) works on it.
+template <int U, class Load, class Proc>
+__device__ __forceinline__ void sweep_rows(int ny, Load ld, Proc pr) {
+  for (int j0 = 0; j0 < ny; j0 += U) {
+    decltype(ld(0)) r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) r[u] = ld(min(j0 + u, ny - 1));        // clamped: a harmless reload
+    __syncwarp();          // both lanes of a mode hold their rows before either overwrites shared pivots
+#pragma unroll
+    for (int u = 0; u < U; u++) if (j0 + u < ny) pr(j0 + u, r[u]);
+  }
+}
+
 template <typename T>
 __device__ void d1_solve(const PArgs<T>& a, const Mode& md, const T* __restrict__ in, T* __restrict__ out, double* s) {
   const long st = 2 * a.M; const int ny = a.ny;
@@ -219,32 +246,6 @@ __device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, 
 }
 
 // phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
-#ifndef PU1
-#define PU1 6
-#define PU2 8
-#define PU3 3
-#define PU4 8
-#define PU5 8
-#define PU6 8
-#define PU7 8
-#endif
-// Sweep driver of pencil_post.  A thread's rows are strictly sequential, and the hardware issues in
-// order, so with "load row j+1, then work on row j" only ONE row of loads is in flight per thread and a
-// pass costs one memory latency per row (the ablation in profiles/r01_post_passes.txt: the passes with
-// few bytes per row ran at 2-4 TB/s).  Here the loads of U rows are issued back to back, then the U
-// dependent row updates follow.  ld(jj) returns the loaded row jj of the sweep, pr(jj, row) works on it.
-template <int U, class Load, class Proc>
-__device__ __forceinline__ void sweep_rows(int ny, Load ld, Proc pr) {
-  for (int j0 = 0; j0 < ny; j0 += U) {
-    decltype(ld(0)) r[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) r[u] = ld(min(j0 + u, ny - 1));        // clamped: a harmless reload
-    __syncwarp();          // both lanes of a mode hold their rows before either overwrites shared pivots
-#pragma unroll
-    for (int u = 0; u < U; u++) if (j0 + u < ny) pr(j0 + u, r[u]);
-  }
-}
-
 template <typename T>
 __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
                            T* phi, T* v, T* dv, double dvm, double dvp) {
@@ -276,80 +277,84 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
 // pencil_pre: (dv, g, v, <u>) -> u, w, omega_x, omega_y, omega_z
 // =================================================================================
 template <typename T>
-__global__ void __launch_bounds__(128) pencil_pre_kernel(PArgs<T> a) {
+__global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut po) {
   typedef typename Vec2<T>::type T2;
   Mode md; Wave<T> wv;
   if (!setup(a, md, wv)) return;
-  const long st = 2 * a.M; const int ny = a.ny; const int c = md.c;
+  const long st = 2 * a.M, M = a.M; const int ny = a.ny; const int c = md.c; const long e = md.e;
+  const int top = ny - 1;
   const bool with_mean = md.zero_mode && a.use_mean;
-  const Prefetch pf(ny);
-  // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w   (two rows of loads in flight)
+  const bool omega = a.op == OP_OMEGA;                 // operator-level calcOmega: u, w are given
+  const int sst = 32;                                  // warp-tiled scratch, see pencil_post
+  double* const sA0 = a.sA + (e >> 5) * 32 * ny + (e & 31);
+  double* const sB0 = a.sB + (e >> 5) * 32 * ny + (e & 31);
+  const T2* const f0 = (omega ? a.u : a.dv) + md.m; const T2* const f1 = (omega ? a.w : a.g) + md.m;
+  // pass 1 (up): u, w on the fly -> eliminate d/dy u, d/dy w
   {
-    ElimD1 eu, ew;
-    const bool omega = a.op == OP_OMEGA;
-    T2 z0 = omega ? mk0<T2>() : a.dv[md.m], z1 = omega ? mk0<T2>() : a.g[md.m];
-    T r0 = omega ? ((const T*)a.u)[md.e] : (T)0, r1 = omega ? ((const T*)a.w)[md.e] : (T)0;
-    for (int j = 0; j < ny; j++) {
-      long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
-      if (!omega) { pf(a.dv + cm, a.M, j, 1); pf(a.g + cm, a.M, j, 1); }
-      T2 z0n = z0, z1n = z1; T r0n = r0, r1n = r1;
-      if (j + 1 < ny) {
-        if (omega) { r0n = ((const T*)a.u)[re + st]; r1n = ((const T*)a.w)[re + st]; }
-        else { z0n = a.dv[cm + a.M]; z1n = a.g[cm + a.M]; }
-      }
-      T u, w;
-      if (omega) { u = r0; w = r1; }
-      else {
-        uw_comp<T, T2>(wv, md, md.zero_mode, z0, z1, c, u, w);
-        if (with_mean) u = c ? (T)0 : a.mean_u[j];                 // writeUmean (nonLinear.c:19-21)
-      }
-      eu.step(a.yt.d1[0], 0, j, ny, (double)u, a.sA, st, md.e);
-      ew.step(a.yt.d1[0], 0, j, ny, (double)w, a.sB, st, md.e);
-      z0 = z0n; z1 = z1n; r0 = r0n; r1 = r1n;
-    }
+    ElimD1P eu, ew;
+    struct Row { T2 a0, a1; };
+    sweep_rows<4>(ny,
+      [&](int j) { Row r; r.a0 = f0[(long)j * M]; r.a1 = f1[(long)j * M]; return r; },
+      [&](int j, const Row& r) {
+        T u, w;
+        if (omega) { u = own<T2, T>(r.a0, c); w = own<T2, T>(r.a1, c); }
+        else {
+          uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c, u, w);
+          if (with_mean) u = c ? (T)0 : a.mean_u[j];                 // writeUmean (nonLinear.c:19-21)
+        }
+        eu.step(a.yt.d1[0], j, ny, (double)u, sA0 + j * sst, sst);
+        ew.step(a.yt.d1[0], j, ny, (double)w, sB0 + j * sst, sst);
+      });
   }
+  if (a.dbg_stop == 7) return;
   // pass 2 (down): back-substitute, build omega (calcOmegakernel, convolution_kernels.cu:46-53)
   {
     double xu = 0.0, xw = 0.0;
-    const bool omega = a.op == OP_OMEGA;
+    const T2* const fv = a.v + md.m;
     struct Row { double dA, dB; T2 v, a0, a1; };       // a0,a1 = (dv,g) or (u,w) of the row
-    Row r;
-    { long cm = (long)(ny - 1) * a.M + md.m, re = (long)(ny - 1) * st + md.e;
-      r.dA = a.sA[re]; r.dB = a.sB[re]; r.v = a.v[cm];
-      r.a0 = omega ? a.u[cm] : a.dv[cm]; r.a1 = omega ? a.w[cm] : a.g[cm]; }
-    for (int j = ny - 1; j >= 0; j--) {
-      long cm = (long)j * a.M + md.m, re = (long)j * st + md.e;
-      pf(a.sA + re, st, j, -1); pf(a.sB + re, st, j, -1); pf(a.v + cm, a.M, j, -1);
-      if (!omega) { pf(a.dv + cm, a.M, j, -1); pf(a.g + cm, a.M, j, -1); }
-      Row n = r;
-      if (j > 0) {
-        n.dA = a.sA[re - st]; n.dB = a.sB[re - st]; n.v = a.v[cm - a.M];
-        n.a0 = omega ? a.u[cm - a.M] : a.dv[cm - a.M]; n.a1 = omega ? a.w[cm - a.M] : a.g[cm - a.M];
-      }
-      double cp = __ldg(a.yt.d1[0].cp + j);
-      xu = r.dA - cp * xu; xw = r.dB - cp * xw;
-      T dudy = (T)xu, dwdy = (T)xw;
-      T u, w, up, wp;
-      if (omega) {
-        u = own<T2, T>(r.a0, c); up = other<T2, T>(r.a0, c); w = own<T2, T>(r.a1, c); wp = other<T2, T>(r.a1, c);
-      } else {
-        uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c, u, w);
-        uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c ^ 1, up, wp);
-        if (with_mean) { u = c ? (T)0 : a.mean_u[j]; up = c ? a.mean_u[j] : (T)0; }
-      }
-      T vp = other<T2, T>(r.v, c);
-      T s = wv.sc;
-      T o1 = dwdy - s * wv.k3 * vp;                    // omega_x = dw/dy - i k3 v
-      T o2 = s * (wv.k3 * up - wv.k1 * wp);            // omega_y = i (k3 u - k1 w)
-      T o3 = -dudy + s * wv.k1 * vp;                   // omega_z = -du/dy + i k1 v
-      if (!omega) { ((T*)a.u)[re] = u; ((T*)a.w)[re] = w; }
-      ((T*)a.ox)[re] = o1; ((T*)a.oy)[re] = o2; ((T*)a.oz)[re] = o3;
-      if (md.zero_mode && c == 0 && a.sc) {            // readUtau (convolution.c:14-16)
-        if (j == 0) a.sc->dudy_wall[0] = (double)dudy;
-        if (j == ny - 1) a.sc->dudy_wall[1] = (double)dudy;
-      }
-      r = n;
-    }
+    sweep_rows<4>(ny,
+      [&](int jj) {
+        const int j = top - jj; Row r;
+        r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.v = fv[(long)j * M]; r.a0 = f0[(long)j * M]; r.a1 = f1[(long)j * M];
+        return r;
+      },
+      [&](int jj, const Row& r) {
+        const int j = top - jj;
+        double cp = __ldg(a.yt.d1[0].cp + j);
+        xu = r.dA - cp * xu; xw = r.dB - cp * xw;
+        T dudy = (T)xu, dwdy = (T)xw;
+        T u, w, up, wp;
+        if (omega) {
+          u = own<T2, T>(r.a0, c); up = other<T2, T>(r.a0, c); w = own<T2, T>(r.a1, c); wp = other<T2, T>(r.a1, c);
+        } else {
+          uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c, u, w);
+          uw_comp<T, T2>(wv, md, md.zero_mode, r.a0, r.a1, c ^ 1, up, wp);
+          if (with_mean) { u = c ? (T)0 : a.mean_u[j]; up = c ? a.mean_u[j] : (T)0; }
+        }
+        T vp = other<T2, T>(r.v, c);
+        T s = wv.sc;
+        T o1 = dwdy - s * wv.k3 * vp;                    // omega_x = dw/dy - i k3 v
+        T o2 = s * (wv.k3 * up - wv.k1 * wp);            // omega_y = i (k3 u - k1 w)
+        T o3 = -dudy + s * wv.k1 * vp;                   // omega_z = -du/dy + i k1 v
+        if (po.nranks > 1) {
+          // multi-GPU: row j goes straight into the receive buffer of the rank that owns plane j (an NVLink
+          // store for the other ranks) - the pencil -> plane transpose of channel_cuda_mpi.c:95-128
+          int p = 0;
+#pragma unroll
+          for (int i = 1; i < 8; i++) p += (i < po.nranks && j >= po.part_j[i]) ? 1 : 0;
+          long idx = 2 * (po.src_off[p] + (long)(j - po.part_j[p]) * M) + e;
+          ((T*)po.rcv[p][0])[idx] = u; ((T*)po.rcv[p][1])[idx] = own<T2, T>(r.v, c); ((T*)po.rcv[p][2])[idx] = w;
+          ((T*)po.rcv[p][3])[idx] = o1; ((T*)po.rcv[p][4])[idx] = o2; ((T*)po.rcv[p][5])[idx] = o3;
+        } else {
+          const long re = (long)j * st + e;
+          if (!omega) { ((T*)a.u)[re] = u; ((T*)a.w)[re] = w; }
+          ((T*)a.ox)[re] = o1; ((T*)a.oy)[re] = o2; ((T*)a.oz)[re] = o3;
+        }
+        if (md.zero_mode && c == 0 && a.sc) {            // readUtau (convolution.c:14-16)
+          if (j == 0) a.sc->dudy_wall[0] = (double)dudy;
+          if (j == ny - 1) a.sc->dudy_wall[1] = (double)dudy;
+        }
+      });
   }
 }
 
@@ -579,7 +584,8 @@ template <typename T>
 static int pre_t(chan_handle* h) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   long nchain = 2 * h->d.M;
-  pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a);
+  PeerOut po; fill_peer_out(h, po);
+  pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, po);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
@@ -602,7 +608,7 @@ static int op_t(chan_handle* h, int op, void* f0, void* f1, void* f2, double bet
   a.op = op; a.f0 = (T2*)f0; a.f1 = (T2*)f1; a.f2 = (T2*)f2; a.op_betha = (T)betha; a.op_dt = (T)dt;
   long nchain = 2 * h->d.M;
   unsigned grid = (unsigned)((nchain + 127) / 128);
-  if (op == OP_OMEGA) { a.use_mean = 0; pencil_pre_kernel<T><<<grid, 128, 0, h->stream>>>(a); }
+  if (op == OP_OMEGA) { a.use_mean = 0; PeerOut po; memset(&po, 0, sizeof(po)); po.nranks = 1; pencil_pre_kernel<T><<<grid, 128, 0, h->stream>>>(a, po); }
   else op_kernel<T><<<grid, 128, 0, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());

@@ -247,6 +247,7 @@ __device__ __forceinline__ bool setup_seg(const PArgs<T>& a, int cb, Mode& md, W
   md.zero_mode = (md.kxi == 0 && md.kzi == 0);
   wv.k1 = a.k1fac * (T)md.kxi; wv.k3 = a.k3fac * (T)md.kzi;
   wv.kk = wv.k1 * wv.k1 + wv.k3 * wv.k3;
+  wv.rkk = md.zero_mode ? (T)1 : (T)1 / wv.kk;
   double k1d = (double)a.k1fac * (double)md.kxi, k3d = (double)a.k3fac * (double)md.kzi;
   wv.kkd = k1d * k1d + k3d * k3d;
   wv.sc = md.c ? (T)1 : (T)-1; wv.sp = -wv.sc;
@@ -503,15 +504,7 @@ static int launch_seg(chan_handle* h, bool post, int n) {
     pencil_post_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st);
   } else {
     CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    PeerOut po; memset(&po, 0, sizeof(po));
-    po.nranks = h->peer_ready ? h->cfg.size : 1;
-    if (h->peer_ready) {
-      for (int p = 0; p <= h->cfg.size; p++) po.part_j[p] = h->part_j[p];
-      for (int p = 0; p < h->cfg.size; p++) {
-        po.src_off[p] = (long)(h->part_j[p + 1] - h->part_j[p]) * h->d.ikx0 * h->d.Kz;
-        for (int f = 0; f < 6; f++) po.rcv[p][f] = h->peer_rcv[p][f];
-      }
-    }
+    PeerOut po; fill_peer_out(h, po);
     pencil_pre_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st, po);
   }
   h->launches++;

@@ -2,6 +2,7 @@
 // thread per real chain, sequential sweeps through fp64 scratch) and kernels_pencil_seg.cu (one
 // thread per (chain, y-segment), everything in registers).
 #pragma once
+#include <string.h>
 #include "chan_internal.h"
 
 namespace chan {
@@ -32,7 +33,7 @@ struct Mode {
 };
 
 template <typename T>
-struct Wave { T k1, k3, kk; double kkd; T sc; T sp; };   // sc = sign of own component of i*z: -1 (re), +1 (im)
+struct Wave { T k1, k3, kk, rkk; double kkd; T sc; T sp; };   // rkk = 1/kk (1 for the mean mode)   // sc = sign of own component of i*z: -1 (re), +1 (im)
 
 template <typename T>
 __device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) {
@@ -46,6 +47,7 @@ __device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) 
   wv.k1 = a.k1fac * (T)md.kxi;
   wv.k3 = a.k3fac * (T)md.kzi;
   wv.kk = wv.k1 * wv.k1 + wv.k3 * wv.k3;
+  wv.rkk = md.zero_mode ? (T)1 : (T)1 / wv.kk;
   double k1d = (double)a.k1fac * (double)md.kxi, k3d = (double)a.k3fac * (double)md.kzi;
   wv.kkd = k1d * k1d + k3d * k3d;
   wv.sc = md.c ? (T)1 : (T)-1;
@@ -105,17 +107,36 @@ __device__ __forceinline__ BcFun bc_functions(const BcCoef& k, double y, int c) 
 template <typename T, typename T2>
 __device__ __forceinline__ void uw_comp(const Wave<T>& wv, const Mode& md, bool zero_mode, const T2& dvz, const T2& gz, int c,
                                         T& u, T& w) {
-  T kk = zero_mode ? (T)1 : wv.kk;
   T s = c ? (T)1 : (T)-1;
   T dp = other<T2, T>(dvz, c), gp = other<T2, T>(gz, c);
-  // u = i (k1 dv - k3 g)/kk ; w = i (k3 dv + k1 g)/kk, written in the reference's operation order
-  u = s * (wv.k1 * dp - wv.k3 * gp) / kk;
-  w = s * (wv.k3 * dp + wv.k1 * gp) / kk;
+  // u = i (k1 dv - k3 g)/kk ; w = i (k3 dv + k1 g)/kk, written in the reference's operation order.  In
+  // double the six divisions per chain row were the bulk of the `pre` kernels' instructions: multiply by
+  // the per-thread reciprocal instead (last-bit difference); the cheap float division stays exact.
+  if (sizeof(T) == 8) {
+    u = s * (wv.k1 * dp - wv.k3 * gp) * wv.rkk;
+    w = s * (wv.k3 * dp + wv.k1 * gp) * wv.rkk;
+  } else {
+    T kk = zero_mode ? (T)1 : wv.kk;
+    u = s * (wv.k1 * dp - wv.k3 * gp) / kk;
+    w = s * (wv.k3 * dp + wv.k1 * gp) / kk;
+  }
   if (zero_mode) { u = 0; w = 0; }
 }
 
 
 template <typename T>
 void fill_pencil_args(chan_handle* h, PArgs<T>& a);
+
+// where the `pre` kernels deliver their rows: locally, or straight into the plane owners' receive buffers
+static inline void fill_peer_out(chan_handle* h, PeerOut& po) {
+  memset(&po, 0, sizeof(po));
+  po.nranks = h->peer_ready ? h->cfg.size : 1;
+  if (!h->peer_ready) return;
+  for (int p = 0; p <= h->cfg.size; p++) po.part_j[p] = h->part_j[p];
+  for (int p = 0; p < h->cfg.size; p++) {
+    po.src_off[p] = (long)(h->part_j[p + 1] - h->part_j[p]) * h->d.ikx0 * h->d.Kz;
+    for (int f = 0; f < 6; f++) po.rcv[p][f] = h->peer_rcv[p][f];
+  }
+}
 
 }  // namespace chan
