@@ -129,15 +129,31 @@ template <int R, int SIGN, class T2> FFT_HD void apply_twiddles(T2* a, const T2*
 // sk divides the span m of every stage but the m = 1 stage, where all rows of a butterfly share one skew.
 FFT_HD int skew_of(int row, int sk, float rsk) { return sk ? (int)(((float)row + 0.5f) * rsk) : 0; }
 
+// Division of a work-item index by a launch-time constant.  The generic integer divisions of the index
+// arithmetic were ~15 % of the z kernel's instructions (ncu source view); with M = floor(2^32/d) + 1 the
+// quotient (b*M) >> 32 is exact for 0 <= b < 2^16 and 1 < d < 2^16 (M = 0 encodes d = 1).  All numerators
+// here are element counts of one shared-memory tile (< 14080 elements, see launch_z / launch_x).
+struct FastDiv { unsigned d, M; };
+inline FastDiv make_fastdiv(int d) { FastDiv f; f.d = (unsigned)d; f.M = d > 1 ? (unsigned)(0x100000000ull / (unsigned)d) + 1u : 0u; return f; }
+FFT_HD int fd_div(int b, FastDiv f) {
+#ifdef __CUDA_ARCH__
+  return f.M ? (int)__umulhi((unsigned)b, f.M) : b;
+#else
+  return f.M ? (int)(((unsigned long long)(unsigned)b * f.M) >> 32) : b;
+#endif
+}
+FFT_HD void fd_divmod(int b, FastDiv f, int& q, int& r) { q = fd_div(b, f); r = b - q * (int)f.d; }
+
 template <class T2, int R, int SIGN, bool DIT>
-FFT_HD void smem_stage(T2* s, int n, int m, int st, int nlines, int nact, int nper, const T2* tw, int tid, int nthr, int sk = 0) {
-  const int nb = n / R, tws = n / (m * R);
+FFT_HD void smem_stage(T2* s, int n, FastDiv fm, int st, FastDiv flines, int nact, int nper, const T2* tw, int tid, int nthr, int sk = 0) {
+  const int m = (int)fm.d, nlines = (int)flines.d;
+  const int nb = n / R, tws = nb / m;
   const float rsk = sk ? 1.0f / (float)sk : 0.0f;
-  const int qst = m * st + ((sk && m >= sk) ? m / sk : 0);
+  const int qst = m * st + ((sk && m >= sk) ? skew_of(m, sk, rsk) : 0);
   for (int b = tid; b < nb * nlines; b += nthr) {
-    int l = b % nlines, bf = b / nlines;
-    int li = (l / nact) * nper + l % nact;
-    int g = bf / m, k = bf - g * m;
+    int l, bf; fd_divmod(b, flines, bf, l);
+    int li = nact == nper ? l : (l / nact) * nper + l % nact;
+    int g, k; fd_divmod(bf, fm, g, k);
     const int row0 = g * m * R + k;
     T2* p = s + (size_t)row0 * st + skew_of(row0, sk, rsk) + li;
     T2 a[R];
@@ -148,6 +164,25 @@ FFT_HD void smem_stage(T2* s, int n, int m, int st, int nlines, int nact, int np
     if (!DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
 #pragma unroll
     for (int q = 0; q < R; q++) p[(size_t)q * qst] = a[q];
+  }
+}
+
+// x transforms: the lines of a tile are a compile-time count (TK), the rows carry no skew
+template <class T2, int R, int SIGN, bool DIT, int TK>
+FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
+  const int nb = n / R, tws = n / (m * R);
+  for (int b = tid; b < nb * TK; b += nthr) {
+    int l = b % TK, bf = b / TK;
+    int g = bf / m, k = bf - g * m;
+    T2* p = s + (size_t)(g * m * R + k) * TK + l;
+    T2 a[R];
+#pragma unroll
+    for (int q = 0; q < R; q++) a[q] = p[(size_t)q * m * TK];
+    if (DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
+    Dft<R, SIGN, T2>::run(a);
+    if (!DIT) apply_twiddles<R, SIGN, T2>(a, tw, k, tws);
+#pragma unroll
+    for (int q = 0; q < R; q++) p[(size_t)q * m * TK] = a[q];
   }
 }
 

@@ -43,6 +43,9 @@ struct XArgs {
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
+__device__ __forceinline__ FastDiv plan_span(const FftPlan& p, int t) { FastDiv f; f.d = (unsigned)p.span[t]; f.M = p.span_magic[t]; return f; }
+
+
 // x inverse: compact spectral rows -> (zero pad) -> natural-order physical x line, still spectral in z
 template <typename T, int TK>
 __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
   FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
   __syncthreads();
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.px.radix[t], a.px.span[t], TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage_x<T2, +1, true, TK>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
   FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
 }
 
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
   FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
-  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage<T2, -1, false>(s, pl, a.px.radix[t], a.px.span[t], TK, TK, TK, TK, tid, nthr); __syncthreads(); }
+  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage_x<T2, -1, false, TK>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
   FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
@@ -83,6 +86,7 @@ struct ZArgs {
   T2* Q; FftPlan pz;
   int dbg_stop;                    // >0: timing ablation only (CHAN_TUNE_Z_STOP): return after phase N
   int nx, nzp, Kz, pb, j_start, XP, SS;   // SS: shared-memory elements per position (>= XP*NIN)
+  FastDiv f_lin, f_lout, f_ng, f_mid, f_kz;   // lines in / out, n/r_first, n/r_last, Kz (index arithmetic without divisions)
   T n2;                            // (T)N2: the reference divides by the int N2 (convolution_kernels.cu:107-121)
   unsigned long long* umax_bits;   // 3 slots
   T* phys; int nz, j_glob0;        // export only: real [NY][NX][2NZ]
@@ -98,7 +102,8 @@ __global__ void __launch_bounds__(256, ZMINB) zstage_kernel(ZArgs<T> a) {
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
   T2* s = (T2*)smem_raw;
-  __shared__ double red[3][8];
+  __shared__ unsigned long long red[3];
+  if (threadIdx.x < 3) red[threadIdx.x] = 0ull;          // barriers follow before its use
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int xp0 = blockIdx.x * a.XP, jb = blockIdx.y;
   if (a.dbg_stop == 9) return;
@@ -107,37 +112,38 @@ __global__ void __launch_bounds__(256, ZMINB) zstage_kernel(ZArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.pz);
   const size_t fstride = (size_t)a.pb * a.nx * a.Kz;
   T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
-  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
   if (a.dbg_stop == 1) return;
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], a.pz.span[t], a.SS, ST, ST, ST, tid, nthr, pl.r_first); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.SS, a.f_lin, ST, ST, tid, nthr, pl.r_first); __syncthreads(); }
   if (a.dbg_stop == 2) return;
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
   if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
   switch (pl.r_last) {
-    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
   if (MODE == ZM_EXPORT) return;
   if (a.dbg_stop == 3) return;
   if (MODE == ZM_ROTOR) {      // block max -> one atomic per block and component
+    // values are >= 0, so the bit pattern orders like the value: warp maximum of the high words, then of
+    // the low words among the lanes that hold it (two redux instead of ten 64-bit shuffle steps)
 #pragma unroll
     for (int c = 0; c < 3; c++) {
-      double v = (double)um[c];
-      for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-      if ((tid & 31) == 0) red[c][tid >> 5] = v;
+      const double v = (double)um[c];
+      const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+      const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+      const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+      if ((tid & 31) == 0) atomicMax(&red[c], ((unsigned long long)mh << 32) | ml);
     }
   }
   __syncthreads();
-  if (MODE == ZM_ROTOR && tid < 3) {
-    double v = 0; for (int wi = 0; wi < (nthr >> 5); wi++) v = fmax(v, red[tid][wi]);
-    atomic_max_pos(a.umax_bits + tid, v);
-  }
-  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], a.pz.span[t], a.SS, a.XP * NOUT, NOUT, NOUT, tid, nthr, pl.r_first); __syncthreads(); }
+  if (MODE == ZM_ROTOR && tid < 3) atomicMax(a.umax_bits + tid, red[tid]);
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.SS, a.f_lout, NOUT, NOUT, tid, nthr, pl.r_first); __syncthreads(); }
   if (a.dbg_stop == 4) return;
-  z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr);
+  z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SS, nxp_valid, tid, nthr);
 }
 
 // -------------------------------------------------------------------------------
@@ -189,6 +195,8 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   size_t sm = ((size_t)n * ss + n / h->pz.radix[0]) * sizeof(T2);      // rows + their skew (plane_core.cuh)
   if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
   a.XP = xp; a.SS = ss;
+  a.f_lin = make_fastdiv(xp * nin); a.f_lout = make_fastdiv(xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1)));
+  a.f_ng = make_fastdiv(n / h->pz.r_first); a.f_mid = make_fastdiv(m); a.f_kz = make_fastdiv(h->d.Kz);
   CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   dim3 grid((h->d.nx / 2 + xp - 1) / xp, pb);
   zstage_kernel<T, MODE><<<grid, threads, sm, h->stream>>>(a);

@@ -13,6 +13,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include "chan_internal.h"
+#include "fft_core.cuh"
 
 namespace chan {
 
@@ -138,7 +139,8 @@ void make_plan(FftPlan* p, int n, bool small_last, int max_radix) {
     int v = best[li]; for (int i = li; i + 1 < ns; i++) best[i] = best[i + 1]; best[ns - 1] = v;
   }
   int span = 1;
-  for (int i = 0; i < ns; i++) { p->radix[i] = best[i]; p->span[i] = span; span *= best[i]; }
+  for (int i = 0; i < ns; i++) { p->radix[i] = best[i]; p->span[i] = span; p->span_magic[i] = fft::make_fastdiv(span).M; span *= best[i]; }
+  p->r_first = ns ? p->radix[0] : 0; p->r_last = ns ? p->radix[ns - 1] : 0;
 }
 
 template <typename T>

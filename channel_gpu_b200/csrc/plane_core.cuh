@@ -24,24 +24,38 @@ namespace fft {
 template <class T2> struct PlanT { int n, nstage, r_first, r_last; const T2* tw; const int* inv; const int* pos; };
 
 template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
-  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage; q.r_first = p.radix[0]; q.r_last = p.radix[p.nstage - 1];
+  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage; q.r_first = p.r_first; q.r_last = p.r_last;
   q.tw = (const T2*)p.tw; q.inv = p.inv; q.pos = p.pos;
   return q;
 }
 
-FFT_HD int seg_index(const SegMap& sm, int ikx) {
-  int sg = 0;
+// Offset of (plane jl, active-kx row ikx) in a plane-side buffer made of per-source blocks (SegMap).  The
+// SegMap lives in the kernel parameters: it is only ever indexed with compile-time constants (a select
+// chain over the segments) - a per-thread index would turn every lookup into a long-latency LDC in the
+// middle of the address computation of the loads (18 % of xfft_inv's stall samples in the ncu source view).
+FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz, int* seg_out = 0) {
+  long base = sm.base[0]; int width = sm.width[0], start = sm.start[0], sg = 0;
+  if (sm.nseg > 1) {
 #pragma unroll
-  for (int i = 1; i < 8; i++) sg += (i < sm.nseg && ikx >= sm.start[i]) ? 1 : 0;
-  return sg;
+    for (int i = 1; i < 8; i++)
+      if (i < sm.nseg && ikx >= sm.start[i]) { base = sm.base[i]; width = sm.width[i]; start = sm.start[i]; sg = i; }
+  }
+  if (seg_out) *seg_out = sg;
+  return (size_t)base + ((size_t)jl * width + (ikx - start)) * Kz;
 }
-FFT_HD size_t seg_offset_in(const SegMap& sm, int sg, int jl, int ikx, int Kz) {
-  return (size_t)sm.base[sg] + ((size_t)jl * sm.width[sg] + (ikx - sm.start[sg])) * Kz;
-}
-FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz) { return seg_offset_in(sm, seg_index(sm, ikx), jl, ikx, Kz); }
+template <class T2> struct SegDst;
+template <class T2> FFT_HD T2* seg_ptr(const SegDst<T2>& d, int nseg, int sg);
 // destination of the forward store: one base pointer per kx segment (= per destination rank when the
 // store goes straight into the peers' pencil-side fields over NVLink; all equal otherwise)
 template <class T2> struct SegDst { T2* p[8]; };
+template <class T2> FFT_HD T2* seg_ptr(const SegDst<T2>& d, int nseg, int sg) {
+  T2* p = d.p[0];
+  if (nseg > 1) {
+#pragma unroll
+    for (int i = 1; i < 8; i++) if (sg == i) p = d.p[i];
+  }
+  return p;
+}
 
 // =================================== x direction =================================================
 // shared layout: s[pos*TK + t], t = kz within the tile (batch-fastest: conflict-free at every stride)
@@ -123,8 +137,8 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
         if (ikx >= 0) {
           T2 v = a[p];
           if (scale != 0) { v.x /= scale; v.y /= scale; }
-          int sg = seg_index(sm, ikx);
-          dst.p[sg][seg_offset_in(sm, sg, jl, ikx, Kz) + kz] = v;
+          int sg; const size_t off = seg_offset(sm, jl, ikx, Kz, &sg);
+          seg_ptr<T2>(dst, sm.nseg, sg)[off + kz] = v;
         }
       }
     }
@@ -132,8 +146,13 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
 template <class T2, int SIGN, bool DIT>
-FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, int m, int st, int nlines, int nact, int nper, int tid, int nthr, int sk = 0) {
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, m, st, nlines, nact, nper, pl.tw, tid, nthr, sk)));
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int sk = 0) {
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, sk)));
+}
+
+template <class T2, int SIGN, bool DIT, int TK>
+FFT_HD void plan_stage_x(T2* s, const PlanT<T2>& pl, int r, int m, int tid, int nthr) {
+  FFT_DISPATCH_RADIX(r, (smem_stage_x<T2, RR, SIGN, DIT, TK>(s, pl.n, m, pl.tw, tid, nthr)));
 }
 
 // =================================== z direction =================================================
@@ -167,14 +186,15 @@ FFT_HD T2 z_packed_combine(T2 A, T2 B, int k, int kind) {
 // inverse, stage 0 fused with the packing load.  q0 -> Q[field 0][plane][x = 2*xp0][0]; fields are
 // fstride apart, x rows Kz apart.
 template <class T2, int R, int NIN>
-FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
-  const int n = pl.n, ng = n / R, ST = XP * NIN;
+FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fng, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
+  const int n = pl.n, ng = (int)fng.d, ST = XP * NIN;
   // lanes run over the groups g: for a fixed input q the natural indices inv[g*R] + q*ng of the ng groups
   // are a permutation of ng CONSECUTIVE kz, so a warp's load is one contiguous piece of a spectral row
   // (lanes over the lines instead would touch one 32-byte sector per lane); the shared-memory stores are
   // then R*SS + 1 elements apart, which the row skew makes conflict-free
   for (int b = tid; b < ng * ST; b += nthr) {
-    int g = b % ng, li = b / ng, f = li % NIN, xpl = li / NIN;
+    int g, li; fd_divmod(b, fng, li, g);
+    const int xpl = li / NIN, f = li - xpl * NIN;
     T2 a[R];
     if (xpl < nxp_valid) {
       const T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
@@ -210,20 +230,21 @@ enum { ZM_ROTOR = 0, ZM_IDENTITY = 1, ZM_EXPORT = 2 };
 // read in the same or an earlier round of the loop, so one barrier per round between the reads and the
 // writes is enough.  The host emulation (threads run one after the other) passes a separate s_out.
 template <class T2, int R, int MODE>
-FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
+FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv fmid, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
                         typename RealOf<T2>::type* umax3, typename RealOf<T2>::type* phys, size_t phys_xstride, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
-  const int n = pl.n, m = n / R, sk = pl.r_first;
-  const int ist = m * SS + m / sk;                       // r_0 divides m = n / r_last (nstage >= 2)
+  const int m = (int)fmid.d, sk = pl.r_first;            // m = n / R
+  const float rsk = 1.0f / (float)sk;
+  const int ist = m * SS + skew_of(m, sk, rsk);          // r_0 divides m = n / r_last (nstage >= 2)
   const T rn2 = ((T)1 / n2) * ((T)1 / n2);
   const int nround = (m * XP + nthr - 1) / nthr;
   for (int it = 0; it < nround; it++) {
     const int b = tid + it * nthr;
-    const int k = b % m, xpl = b / m;
+    int k, xpl; fd_divmod(b, fmid, xpl, k);
     const bool work = b < m * XP && xpl < nxp_valid;
-    const size_t row = (size_t)k * SS + k / sk;
+    const size_t row = (size_t)k * SS + skew_of(k, sk, rsk);
     T2 a[NIN][R];
     if (work) {
 #pragma unroll
@@ -281,12 +302,13 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, int XP, 
 // all fall into the same banks (7x the ideal number of wavefronts in the ncu source view).  The
 // pos/r_0 skew of the layout spreads exactly those rows over the banks.
 template <class T2, int NIN, int NOUT>
-FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
+FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fkz, int XP, int SS, int nxp_valid, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
-  const int n = pl.n, sk = pl.r_first;
+  const int n = pl.n, sk = pl.r_first, Kz = (int)fkz.d;
   const float rsk = 1.0f / (float)sk;
   for (int b = tid; b < Kz * NOUT * XP; b += nthr) {
-    int k = b % Kz, l = b / Kz, f = l % NOUT, xpl = l / NOUT;
+    int k, l; fd_divmod(b, fkz, l, k);
+    const int xpl = l / NOUT, f = l - xpl * NOUT;
     if (xpl >= nxp_valid) continue;
     const int pk = FFT_LDG(pl.pos + k), pn = FFT_LDG(pl.pos + (k ? n - k : 0));
     T2 Yk = s[(size_t)pk * SS + skew_of(pk, sk, rsk) + xpl * NOUT + f];

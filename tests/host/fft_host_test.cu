@@ -28,6 +28,12 @@ static double frand() { return 2.0 * rand() / RAND_MAX - 1.0; }
 #define EACH_THREAD for (int tid = 0; tid < NTHR; tid++)
 static const int NTHR = 96;
 
+#define XSTAGE(SIGN, DIT)                                                                                         \
+  switch (TK) {                                                                                                   \
+    case 2: plan_stage_x<T2, SIGN, DIT, 2>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
+    case 4: plan_stage_x<T2, SIGN, DIT, 4>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
+    default: plan_stage_x<T2, SIGN, DIT, 8>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;           \
+  }
 template <class T2> double test_x(int nx, int Kz, int TK) {
   typedef typename RealOf<T2>::type T;
   Host<T2> H; H.build(nx, false);
@@ -43,7 +49,7 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   double err = 0, nrm = 0;
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
-    for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], H.p.span[t], TK, TK, TK, TK, tid, NTHR);
+    for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD XSTAGE(+1, true)
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
   }
   for (int kz = 0; kz < Kz; kz++) for (int x = 0; x < nx; x++) {
@@ -57,7 +63,7 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   SegDst<T2> dsts; for (int i = 0; i < 8; i++) dsts.p[i] = dst.data();
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
-    for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD plan_stage<T2, -1, false>(s.data(), pl, H.p.radix[t], H.p.span[t], TK, TK, TK, TK, tid, NTHR);
+    for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD XSTAGE(-1, false)
     EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
   }
   err = nrm = 0;
@@ -97,18 +103,18 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   T n2 = (T)7.0;
   std::vector<T> phys((size_t)nxrows * (n + 2), (T)0);
   T um[3] = { 0, 0, 0 };
-  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR))); }
-  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], H.p.span[t], SS, ST, ST, ST, tid, NTHR, pl.r_first);
+  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, nxp_valid, Kz, tid, NTHR))); }
+  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), SS, make_fastdiv(ST), ST, ST, tid, NTHR, pl.r_first);
   EACH_THREAD {
     switch (pl.r_last) {
-      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
     }
   }
   if (MODE != ZM_EXPORT) {
-    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], H.p.span[t], SS, XP * NOUT, NOUT, NOUT, tid, NTHR, pl.r_first);
-    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, XP, SS, nxp_valid, Kz, tid, NTHR);
+    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), SS, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR, pl.r_first);
+    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, make_fastdiv(Kz), XP, SS, nxp_valid, tid, NTHR);
   }
   // reference
   double err = 0, nrm = 0, umref[3] = { 0, 0, 0 };
