@@ -195,8 +195,12 @@ def main():
     ap.add_argument("--plane-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile", action="store_true", help="device-timed leg only (for ncu runs)")
+    ap.add_argument("--grid", default="", help="NX,NY,NZ override for kernel experiments (profile runs only)")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
+    if args.grid:
+        gx, gy, gz = (int(v) for v in args.grid.split(","))
+        cfg = dict(nx=gx, ny=gy, nz=gz, name="experiment %dx%dx%d" % (gx, gy, 2 * gz - 2))
     if args.impl == "reference":
         return run_reference(args, cfg)
 

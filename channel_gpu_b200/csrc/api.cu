@@ -72,8 +72,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   h->prec = cfg->precision;
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
-      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 256 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 256 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 } };
+      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 128 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 128 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 } };
     for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
   }
   Dims& d = h->d;
@@ -140,7 +140,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // to fill the GPU with one thread per chain (small grids, many GPUs).
   // y stage: thread-per-chain kernels (batched row loads, HBM-bound) when there are enough chains to fill the
   // SMs, the segment-parallel register kernels when a rank holds few chains (many ranks / small grids)
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = ((2 * d.M < 148L * 192) ? 1 : 0) | ((2 * d.M < 148L * 64) ? 2 : 0);
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256) ? 1 : 0;     // `pre` only: the chain `post` wins at every size measured
+  if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M < 148L * 128) ? 1 : 0;
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;

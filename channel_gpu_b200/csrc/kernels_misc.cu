@@ -80,14 +80,18 @@ struct SArgs {
 // meanUevol.c:86-114; x = rhs in, solution out; a=lower, b=diag, c=upper (c is destroyed)
 template <typename T>
 __device__ void tri_inplace(T* x, int n, const T* a, const T* b, T* c) {
-  c[0] = c[0] / b[0];
-  x[0] = x[0] / b[0];
+  // the recurrences run in registers; the array loads do not depend on them and are hoisted by the unroll
+  T cp = c[0] / b[0], xp = x[0] / b[0];
+  c[0] = cp; x[0] = xp;
+#pragma unroll 4
   for (int i = 1; i < n; i++) {
-    T m = (T)(1.0 / (double)(b[i] - a[i] * c[i - 1]));
-    c[i] = c[i] * m;
-    x[i] = (x[i] - a[i] * x[i - 1]) * m;
+    T m = (T)(1.0 / (double)(b[i] - a[i] * cp));
+    cp = c[i] * m;
+    xp = (x[i] - a[i] * xp) * m;
+    c[i] = cp; x[i] = xp;
   }
-  for (int i = n - 1; i-- > 0;) x[i] = x[i] - c[i] * x[i + 1];
+#pragma unroll 4
+  for (int i = n - 1; i-- > 0;) { xp = x[i] - c[i] * xp; x[i] = xp; }
 }
 
 template <typename T>
@@ -103,7 +107,10 @@ template <typename T>
 __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
   const int ny = a.ny, tid = threadIdx.x, nt = blockDim.x;
   Scalars* sc = a.sc;
-  T* lo = a.tmp; T* cd = lo + ny; T* up = cd + ny; T* aux = up + ny; T* nnew = aux + ny;
+  // work arrays, the mean profile and its increment live in shared memory: the two tridiagonal solves are
+  // serial on one thread, and from global memory every dependent access cost an L2 round trip (87 us per call)
+  extern __shared__ __align__(16) unsigned char scalar_smem[];
+  T* lo = (T*)scalar_smem; T* cd = lo + ny; T* up = cd + ny; T* aux = up + ny; T* nnew = aux + ny; T* su = nnew + ny; T* suw = su + ny;
   const T nx = (T)a.nx, nz = (T)a.nz;
   const T N2 = (T)(a.nx * (2 * a.nz - 2));
   const T DELTA_Y = (T)(2.0f / (float)(ny - 1));
@@ -125,12 +132,14 @@ __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
   }
   if (!a.owns_zero) return;
   const T dt = (T)sc->dt;
+  for (int j = tid; j < ny; j += nt) su[j] = a.u[j];
+  __syncthreads();
 
   // ---- meanURKstep_1 (meanUevol.c:439-464): uw = (alpha+betha) nu d2u/dy2 + dseda N_old
   for (int j = tid; j < ny; j += nt) {
     T A, B, C, al, be; w2_coef<T>(a.ma[j], a.mb[j], A, B, C, al, be);
     up[j] = al; cd[j] = (T)1.0f; lo[j] = be;
-    if (j >= 1 && j < ny - 1) aux[j] = A * a.u[j + 1] + C * a.u[j] + B * a.u[j - 1];
+    if (j >= 1 && j < ny - 1) aux[j] = A * su[j + 1] + C * su[j] + B * su[j - 1];
     nnew[j] = a.H1[(size_t)j * a.M].x;                      // readNmean (meanUevol.c:127-133)
   }
   __syncthreads();
@@ -142,7 +151,7 @@ __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
       T A = (T)6.0f / ((a0 - b0) * ((T)2.0f * a0 - b0));
       T B = (T)-6.0f * a0 / ((a0 * b0 - b0 * b0) * ((T)2.0f * a0 - b0));
       T E = -A - B;
-      aux[0] = E * a.u[0] + A * a.u[1] + B * a.u[2];
+      aux[0] = E * su[0] + A * su[1] + B * su[2];
     }
     {
       T aN = a.mb[ny - 1], bN = a.ma[ny + 1];
@@ -150,7 +159,7 @@ __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
       T A = (T)6.0f / ((aN - bN) * ((T)2.0f * aN - bN));
       T B = (T)-6.0f * aN / ((aN * bN - bN * bN) * ((T)2.0f * aN - bN));
       T E = -A - B;
-      aux[ny - 1] = E * a.u[ny - 1] + A * a.u[ny - 2] + B * a.u[ny - 3];
+      aux[ny - 1] = E * su[ny - 1] + A * su[ny - 2] + B * su[ny - 3];
     }
     tri_inplace<T>(aux, ny, lo, cd, up);
   }
@@ -160,7 +169,7 @@ __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
     T uw = (a.alpha + a.betha) * nu * aux[j] + a.dseda * a.N[j];
     a.N[j] = nnew[j];
     // ---- meanURKstep_2 (meanUevol.c:466-487)
-    a.uw[j] = dt * (uw + a.gammad * nnew[j]);
+    suw[j] = dt * (uw + a.gammad * nnew[j]);
   }
   __syncthreads();
   // implicitStepMeanU (meanUevol.c:347-437)
@@ -172,22 +181,24 @@ __global__ void __launch_bounds__(128) scalar_kernel(SArgs<T> a) {
     if (j == 0 || j == ny - 1) { lo[j] = 0; cd[j] = (T)1.0f; up[j] = 0; }
     if (j == 1) lo[j] = 0;
     if (j == ny - 2) up[j] = 0;
-    aux[j] = (j == 0 || j == ny - 1) ? (T)0.0f : (al * a.uw[j + 1] + a.uw[j] + be * a.uw[j - 1]);
+    aux[j] = (j == 0 || j == ny - 1) ? (T)0.0f : (al * suw[j + 1] + suw[j] + be * suw[j - 1]);
   }
   __syncthreads();
   if (tid == 0) {
     tri_inplace<T>(aux, ny, lo, cd, up);
-    for (int j = 0; j < ny; j++) { a.uw[j] = aux[j]; a.u[j] = a.u[j] + aux[j]; }
+    for (int j = 0; j < ny; j++) { suw[j] = aux[j]; su[j] = su[j] + aux[j]; }
     // forcing (meanUevol.c:201-221): constant flux; the integral starts at j = 10 (Q12)
     T Qt = (T)0.0f;
-    for (int j = 10; j < ny - 1; j++) Qt += (T)0.5f * (a.u[j + 1] + a.u[j]) * a.ma[j];
-    for (int j = 1; j < ny - 1; j++) a.u[j] = a.u[j] + (a.qvel * N2 - Qt) / LY;
+    for (int j = 10; j < ny - 1; j++) Qt += (T)0.5f * (su[j + 1] + su[j]) * a.ma[j];
+    for (int j = 1; j < ny - 1; j++) su[j] = su[j] + (a.qvel * N2 - Qt) / LY;
     // readUtau (meanUevol.c:178-199)
     for (int c = 0; c < 2; c++) {
       T d = (T)sc->dudy_wall[c] / N2;
       sc->utau[c] = (double)(T)sqrt((T)1.0f / a.reynolds * fabs(d));
     }
   }
+  __syncthreads();
+  for (int j = tid; j < ny; j += nt) { a.u[j] = su[j]; a.uw[j] = suw[j]; }
 }
 
 static const float kAlpha[3] = { 29.0f / 96.0f, -3.0f / 40.0f, 1.0f / 6.0f };
@@ -206,7 +217,9 @@ static int scalar_t(chan_handle* h, int n) {
   a.sc = h->sc;
   a.alpha = (T)kAlpha[n]; a.betha = (T)kBetha[n]; a.gammad = (T)kGamma[n]; a.dseda = (T)kDseda[n];
   a.reynolds = (T)(float)h->cfg.reynolds; a.qvel = (T)(float)h->cfg.qvelocity; a.cfl = (T)(float)h->cfg.cfl;
-  scalar_kernel<T><<<1, 128, 0, h->stream>>>(a);
+  const size_t sm = (size_t)7 * h->d.ny * sizeof(T);
+  if (sm > 48 * 1024) CHAN_CUDA(h, cudaFuncSetAttribute(scalar_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  scalar_kernel<T><<<1, 128, sm, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;

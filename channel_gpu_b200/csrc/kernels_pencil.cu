@@ -189,15 +189,6 @@ struct ElimVarP {
 
 // ---- unfused building blocks (operator-level API, calcVdV) -------------------
 // out = d/dy in  (deriv_Y_HO_double, derivatives_nu_double.cu:390-415); in/out are real views [NY][2M]
-#ifndef PU1
-#define PU1 6
-#define PU2 8
-#define PU3 3
-#define PU4 8
-#define PU5 8
-#define PU6 8
-#define PU7 8
-#endif
 // Sweep driver of pencil_post.  A thread's rows are strictly sequential, and the hardware issues in
 // order, so with "load row j+1, then work on row j" only ONE row of loads is in flight per thread and a
 // pass costs one memory latency per row (the ablation in profiles/r01_post_passes.txt: the passes with
@@ -260,7 +251,7 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
   T* const pp = phi + md.e; T* const pv = v + md.e; T* const pd = dv + md.e;
   struct Row { T p, v, d; };
-  sweep_rows<PU7>(ny,
+  sweep_rows<8>(ny,
     [&](int j) { Row r; r.p = pp[(long)j * st]; r.v = pv[(long)j * st]; r.d = pd[(long)j * st]; return r; },
     [&](int j, const Row& r) {
       BcFun f = bc_functions(k, __ldg(a.yt.y + j), md.c);
@@ -361,8 +352,12 @@ __global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut 
 // =================================================================================
 // pencil_post: H1..3, phi, g, R_phi, R_g -> phi, g, v, dv, R_phi, R_g   (7 passes)
 // =================================================================================
-template <typename T>
-__global__ void __launch_bounds__(128, 4) pencil_post_kernel(PArgs<T> a) {
+// DEEP = false: 128 registers, four blocks per SM (a GPU full of chains, bandwidth-bound).
+// DEEP = true: few chains per SM (many ranks, small grids): occupancy is irrelevant and a pass costs one
+// memory latency per batch, so the batches are as deep as 255 registers allow.
+template <typename T, bool DEEP>
+__global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T> a) {
+  constexpr int PU1 = DEEP ? 8 : 6, PU2 = DEEP ? 12 : 8, PU3 = DEEP ? 6 : 3, PU4 = DEEP ? 12 : 8, PU5 = DEEP ? 16 : 8, PU6 = DEEP ? 16 : 8;
   typedef typename Vec2<T>::type T2;
   Mode md; Wave<T> wv;
   if (!setup(a, md, wv)) return;
@@ -595,8 +590,10 @@ static int post_t(chan_handle* h, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
   long nchain = 2 * h->d.M;
-  const int bt = h->tune.post_threads;       // 64 or 128 (setup() derives the chain from blockIdx.x * blockDim.x)
-  pencil_post_kernel<T><<<(unsigned)((nchain + bt - 1) / bt), bt, 0, h->stream>>>(a);
+  const int bt = h->tune.post_deep ? 32 : h->tune.post_threads;   // few chains: one warp per block, spread over all SMs
+  const unsigned grid = (unsigned)((nchain + bt - 1) / bt);
+  if (h->tune.post_deep) pencil_post_kernel<T, true><<<grid, bt, 0, h->stream>>>(a);
+  else pencil_post_kernel<T, false><<<grid, bt, 0, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
