@@ -72,8 +72,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   h->prec = cfg->precision;
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
-      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 128 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 128 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 8 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 } };
+      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 0 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 0 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 0 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 } };
     for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
   }
   Dims& d = h->d;
@@ -101,6 +101,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (cfg->device >= 0) CHAN_CUDA(h, cudaSetDevice(cfg->device));
   CHAN_CUDA(h, cudaGetDevice(&h->device));
   CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   int rc;
   const size_t fb = field_bytes(h);
   void** fields[11] = { &h->phi, &h->g, &h->v, &h->dv, &h->Rphi, &h->Rg, &h->u, &h->w, &h->ox, &h->oy, &h->oz };
@@ -160,6 +163,9 @@ extern "C" void chan_destroy(chan_handle* h) {
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->aux) cudaStreamDestroy(h->aux);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -328,11 +334,26 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if ((rc = (h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
   t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
-  t_end(h, t); t = t_begin(h, CHAN_STAGE_SCALAR);
-  if ((rc = launch_scalar_stage(h, n))) return rc;        // mean flow, calcDt
-  t_end(h, t); t = t_begin(h, CHAN_STAGE_POST);
+  t_end(h, t);
+  // The mean-flow / dt kernel is one block of serial work and shares nothing with pencil_post (it reads
+  // the mean row of H1, the wall shear and the maxima; post reads sc->dt, which only end_step changes):
+  // it runs on the side stream while post fills the GPU, and the main stream joins it afterwards.
+  CHAN_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
+  CHAN_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_fork, 0));
+  {
+    cudaStream_t main_stream = h->stream;
+    h->stream = h->aux;
+    t = t_begin(h, CHAN_STAGE_SCALAR);
+    rc = launch_scalar_stage(h, n);                      // mean flow, calcDt
+    t_end(h, t);
+    h->stream = main_stream;
+    if (rc) return rc;
+  }
+  CHAN_CUDA(h, cudaEventRecord(h->ev_join, h->aux));
+  t = t_begin(h, CHAN_STAGE_POST);
   rc = (h->tune.pencil_seg & 2) ? launch_pencil_post_seg(h, n) : launch_pencil_post(h, n);   // RK explicit + h_v,h_g + implicit + bi-Laplacian
   t_end(h, t);
+  CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
   return rc;
 }
 

@@ -93,6 +93,8 @@ struct chan_handle {
   chan_config cfg;
   int device;
   cudaStream_t stream;
+  cudaStream_t aux;             // side stream: the one-block mean-flow/dt kernel runs beside pencil_post
+  cudaEvent_t ev_fork, ev_join;
   // state + work fields, compact plane-major, complex T
   void *phi, *g, *v, *dv, *Rphi, *Rg;
   void *u, *w, *ox, *oy, *oz;

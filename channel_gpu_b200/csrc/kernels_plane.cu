@@ -147,10 +147,21 @@ __global__ void __launch_bounds__(256, ZMINB) zstage_kernel(ZArgs<T> a) {
 }
 
 // -------------------------------------------------------------------------------
+// kz columns per x-transform block: the widest tile that still lets three blocks share an SM (sweeps
+// at NX = 384 and 1024, profiles/r01_sweeps.txt); whatever fits when NX is so long that no tile does
 static int pick_tk(chan_handle* h, size_t elem) {
-  for (int tk = h->tune.x_tk; tk >= 2; tk >>= 1)
+  const int top = h->tune.x_tk > 0 ? h->tune.x_tk : 8;
+  if (h->tune.x_tk <= 0)
+    for (int tk = top; tk >= 2; tk >>= 1)
+      if ((size_t)h->d.nx * tk * elem <= 72 * 1024) return tk;
+  for (int tk = top; tk >= 2; tk >>= 1)
     if ((size_t)h->d.nx * tk * elem <= 200 * 1024) return tk;
   return 0;
+}
+// 128 threads (four blocks per SM) up to 3072-element tiles, 256 above (measured at NX = 384 and 1024)
+static int pick_x_threads(chan_handle* h, int tk) {
+  if (h->tune.x_threads > 0) return h->tune.x_threads;
+  return h->d.nx * tk >= 4096 ? 256 : 128;
 }
 
 template <typename T, int TK>
@@ -160,10 +171,10 @@ static int launch_x(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
   dim3 grid((h->d.Kz + TK - 1) / TK, pb, nf);
   if (inverse) {
     CHAN_CUDA(h, cudaFuncSetAttribute(xfft_inv_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_inv_kernel<T, TK><<<grid, h->tune.x_threads, sm, h->stream>>>(a);
+    xfft_inv_kernel<T, TK><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
   } else {
     CHAN_CUDA(h, cudaFuncSetAttribute(xfft_fwd_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_fwd_kernel<T, TK><<<grid, h->tune.x_threads, sm, h->stream>>>(a);
+    xfft_fwd_kernel<T, TK><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
@@ -185,10 +196,12 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   // x-pairs per block: enough positions for the register-fused middle stage to occupy the block,
   // bounded by ~96 KB of shared memory so that two blocks fit on an SM
   const int n = h->d.nzp, m = n / h->pz.radix[h->pz.nstage - 1];
-  const int threads = h->tune.z_threads;
-  int xp = h->tune.z_xp > 0 ? h->tune.z_xp : (3 * threads / 4 + m - 1) / m;
+  int xp = h->tune.z_xp > 0 ? h->tune.z_xp : (96 + m - 1) / m;
   while (xp > 1 && (size_t)n * (xp * nin + 1) * sizeof(T2) > 96 * 1024) xp--;
   if (xp > h->d.nx / 2) xp = h->d.nx / 2;
+  // one thread per item of the register-fused middle stage (m positions x xp pairs), within 128..256
+  int threads = h->tune.z_threads;
+  if (threads <= 0) { threads = (m * xp + 31) / 32 * 32; threads = threads < 128 ? 128 : (threads > 256 ? 256 : threads); }
   // an odd number of elements per position keeps the register-fused middle stage (threads stride
   // over positions) free of bank conflicts
   int ss = xp * nin; if (h->tune.z_pad && !(ss & 1)) ss++;
