@@ -79,44 +79,74 @@ def synthetic_fields(nx, ny, nz, cplx, amp=0.12, seed=20261106):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    """SM clock and throttle reasons sampled DURING the timed region: NVML from a thread every 10 ms
+    (the timed region is a fraction of a second, `nvidia-smi -lms` does not even start that fast);
+    nvidia-smi one-shot queries are the fall-back when NVML cannot be loaded."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, gpu=0):
-        self.lines = []; self.p = None; self.gpu = gpu
+        self.gpu = gpu; self.sm = []; self.mx = None; self.reasons = set(); self.run = False; self.t = None; self.how = None
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        bits = {}
+        for name, attr in (("hw_slowdown", "nvmlClocksEventReasonHwSlowdown"), ("hw_thermal_slowdown", "nvmlClocksEventReasonHwThermalSlowdown"),
+                           ("sw_thermal_slowdown", "nvmlClocksEventReasonSwThermalSlowdown"), ("sw_power_cap", "nvmlClocksEventReasonSwPowerCap")):
+            v = getattr(nv, attr, None) or getattr(nv, attr.replace("ClocksEventReason", "ClocksThrottleReason"), None)
+            if v is not None:
+                bits[name] = v
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while self.run:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.hd, nv.NVML_CLOCK_SM)))
+                r = get_reasons(self.hd)
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def _smi_loop(self):
+        while self.run:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.sm.append(float(f[0])); self.mx = float(f[1])
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(name)
+            except Exception:
+                pass
 
     def start(self):
+        self.run = True
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
-                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._rd, daemon=True); self.t.start()
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = self.gpu
+            if vis and all(v.strip().isdigit() for v in vis.split(",")):
+                idx = int(vis.split(",")[self.gpu])
+            self.hd = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.hd, nv.NVML_CLOCK_SM))
+            self.how = "nvml, 10 ms"
+            self.t = threading.Thread(target=self._nvml_loop, daemon=True)
         except Exception:
-            self.p = None
-
-    def _rd(self):
-        for l in self.p.stdout:
-            self.lines.append(l.strip())
+            self.how = "nvidia-smi one-shot queries"
+            self.t = threading.Thread(target=self._smi_loop, daemon=True)
+        self.t.start()
 
     def stop(self):
-        if not self.p:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.p.terminate()
-        sm, mx, reasons = [], [], set()
-        for l in self.lines:
-            f = [x.strip() for x in l.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self.run = False
+        if self.t:
+            self.t.join(timeout=6)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no clock sample"], "samples": 0, "how": self.how}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.mx, "reasons": sorted(self.reasons), "samples": len(self.sm), "how": self.how}
 
 
 def cpu_baseline_sample(cfg, prec):
@@ -270,22 +300,25 @@ def main():
     ch2 = ch
     t0 = time.perf_counter()
     ch2.set_fields(ddv_p, g_p); ch2.set_umean(um)
+    t1 = time.perf_counter()
     ch2.rk_init()
     d2h_scalars = 0
     for _ in range(K):
         ch2.rk_step(1)
         s = ch2.scalars(); d2h_scalars += 96
-    o1, o2 = ch2.get_fields()
+    t2 = time.perf_counter()
+    o1, o2 = ch2.get_fields(out=(out_ddv_t.numpy(), out_g_t.numpy()))
     e2e_s = time.perf_counter() - t0
+    e2e_parts = {"set_fields_ms": 1e3 * (t1 - t0), "init_and_steps_ms": 1e3 * (t2 - t1), "get_fields_ms": 1e3 * (t0 + e2e_s - t2)}
     fb = ddv.nbytes
     e2e = {"value": K / e2e_s, "unit": "steps/s", "h2d_bytes_per_step": int(2 * fb / K), "d2h_bytes_per_step": int((2 * fb + d2h_scalars) / K),
-           "note": "set_fields (pinned H2D + relayout) + rk_init + K x (rk_step + D2H scalars) + get_fields (relayout + D2H); field copies amortised over K steps"}
+           "note": "set_fields (pinned H2D + relayout) + rk_init + K x (rk_step + D2H scalars) + get_fields (relayout + D2H); field copies amortised over K steps", "parts": e2e_parts}
 
     # ---- roofline of the dominant kernel ---------------------------------------------------
     # algorithmic bytes per launch (P = one compact field, Qc = one x-padded field):
     peak, peak_src = measured_peaks()
     P = sz["P"] / world; Qc = sz["Qc"] / world
-    kern = {"pencil_pre": (0, 9 * P), "pencil_post": (3, 13 * P), "xfft_inv": (5, 6 * P + 6 * Qc),
+    kern = {"pencil_pre": (0, (8 if world == 1 else 9) * P), "pencil_post": (3, 13 * P), "xfft_inv": (5, 6 * P + 6 * Qc),
             "zstage": (6, 9 * Qc), "xfft_fwd": (7, 3 * Qc + 3 * P)}
     stages = {}
     for name, (sid, nbytes) in kern.items():

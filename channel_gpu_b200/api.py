@@ -149,8 +149,12 @@ class Channel:
         ddv, g = self._host(ddv), self._host(g)
         self._ck(self.L.chan_set_fields(self.h, ddv.ctypes.data, g.ctypes.data), "chan_set_fields")
 
-    def get_field(self, name):
-        out = np.empty((self.nx, self.nz, self.ny), self.cplx)
+    def get_field(self, name, out=None):
+        """`out`: optional destination (e.g. a view of pinned memory) of the reference shape and dtype."""
+        if out is None:
+            out = np.empty((self.nx, self.nz, self.ny), self.cplx)
+        elif out.shape != (self.nx, self.nz, self.ny) or out.dtype != self.cplx or not out.flags["C_CONTIGUOUS"]:
+            raise ChannelError("out must be a C-contiguous %s array of shape %s" % (np.dtype(self.cplx), (self.nx, self.nz, self.ny)))
         self._ck(self.L.chan_get_field(self.h, FIELDS[name], out.ctypes.data), "chan_get_field")
         return out
 
@@ -158,9 +162,9 @@ class Channel:
         a = self._host(a)
         self._ck(self.L.chan_set_field(self.h, FIELDS[name], a.ctypes.data), "chan_set_field")
 
-    def get_fields(self):
-        """D2H + writeData payload (io.c:37-72)."""
-        return self.get_field("ddv"), self.get_field("g")
+    def get_fields(self, out=None):
+        """D2H + writeData payload (io.c:37-72).  `out`: optional (ddv, g) destination arrays."""
+        return self.get_field("ddv", None if out is None else out[0]), self.get_field("g", None if out is None else out[1])
 
     def set_umean(self, um):
         """readU payload (meanUevol.c:166-176)."""

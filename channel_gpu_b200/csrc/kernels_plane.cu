@@ -22,6 +22,9 @@
 //    Q[f][plane][x][kz] is produced and consumed per plane batch sized to stay
 //    resident in the 126 MB L2.
 #include "plane_core.cuh"
+#ifndef ZMAXT
+#define ZMAXT 256
+#endif
 #ifndef ZMINB
 #define ZMINB 2
 #endif
@@ -97,7 +100,7 @@ __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double 
 }
 
 template <typename T, int MODE>
-__global__ void __launch_bounds__(256, ZMINB) zstage_kernel(ZArgs<T> a) {
+__global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);

@@ -8,7 +8,7 @@ mkdir -p gpurun_out
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
 cat gpurun_out/${TAG}_plain.log | tail -1
 # launch list: skip init + 3 warm-up steps, keep one timed step
-ncu --metrics gpu__time_duration.sum --clock-control none -s ${SKIP:-75} -c ${COUNT:-40} --csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -s ${SKIP:-67} -c ${COUNT:-19} --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1 || echo "ncu launch list failed"
 # full capture of the hot kernels (one launch each, late in the run)
 ncu --set full --clock-control none --import-source on -k regex:"pencil_post|pencil_pre|zstage_kernel|xfft_inv|xfft_fwd" \
