@@ -144,7 +144,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // y stage: thread-per-chain kernels (batched row loads, HBM-bound) when there are enough chains to fill the
   // SMs, the segment-parallel register kernels when a rank holds few chains (many ranks / small grids)
   if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256) ? 1 : 0;     // `pre` only: the chain `post` wins at every size measured
-  if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M < 148L * 128) ? 1 : 0;
+  if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;

@@ -195,8 +195,9 @@ struct ElimVarP {
 // few bytes per row ran at 2-4 TB/s).  Here the loads of U rows are issued back to back, then the U
 // dependent row updates follow.  ld(jj) returns the loaded row jj of the sweep, pr(jj, row) works on it.
 template <int U, class Load, class Proc>
-__device__ __forceinline__ void sweep_rows(int ny, Load ld, Proc pr) {
-  for (int j0 = 0; j0 < ny; j0 += U) {
+__device__ __forceinline__ void sweep_rows(int ny, Load ld, Proc pr, int part = 0, int nparts = 1) {
+  // part / nparts: batches dealt round-robin to cooperating warps (only for passes whose rows are independent)
+  for (int j0 = part * U; j0 < ny; j0 += nparts * U) {
     decltype(ld(0)) r[U];
 #pragma unroll
     for (int u = 0; u < U; u++) r[u] = ld(min(j0 + u, ny - 1));        // clamped: a harmless reload
@@ -239,7 +240,7 @@ __device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, 
 // phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
 template <typename T>
 __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
-                           T* phi, T* v, T* dv, double dvm, double dvp) {
+                           T* phi, T* v, T* dv, double dvm, double dvp, int part = 0, int nparts = 1) {
   const long st = 2 * a.M; const int ny = a.ny;
   if (!((double)dt > 1e-8)) return;                       // bilplacSolver_double.cu:314 (Q6)
   // mode (0,0) is zeroed (:252-262); it runs the same instructions on a dummy kk so that the
@@ -261,7 +262,7 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
       vv = vv + c1 * f.v1 + c2 * f.v2;
       if (md.zero_mode) { ppv = 0.0; vv = 0.0; dd = 0.0; }
       pp[(long)j * st] = (T)ppv; pv[(long)j * st] = (T)vv; pd[(long)j * st] = (T)dd;
-    });
+    }, part, nparts);
 }
 
 // =================================================================================
@@ -494,6 +495,151 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
 }
 
 // =================================================================================
+// pencil_post for ranks that hold few chains (many GPUs, small grids).  One warp per chain runs out of
+// parallelism there: the kernel is then bound by the ~135k dependent instructions a chain executes, not by
+// memory.  Here THREE warps share 32 chains, one role each; the passes already hand their data over through
+// the (L2-resident) scratch, so the roles only meet at a block barrier between passes:
+//   pass   warp 0 (phi)                      warp 1 (g)                    warp 2 (hv)
+//   P1     eliminate phi'                    eliminate g'                  eliminate hv'
+//   P2     phi' -> eliminate phi''           g' -> eliminate g''           hv'
+//   P3     phi'' , RK update, implicit elim. g'', RK update, implicit el.  -
+//   P4     phi_new, Helmholtz elimination    g_new                         -
+//   P5-6   v, dv                             -                             -
+//   P7     wall correction, rows dealt round-robin to the three warps
+// Same arithmetic in the same order per chain as pencil_post_kernel (bit-identical results).  The Helmholtz
+// pivots go to sC (free after P3) because warp 1 still reads the implicit pivots in sP during P4.
+// =================================================================================
+template <typename T>
+__global__ void __launch_bounds__(96, 2) pencil_post_roles_kernel(PArgs<T> a) {
+  typedef typename Vec2<T>::type T2;
+  __shared__ double wall[2][32];
+  const int role = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  Mode md; Wave<T> wv;
+  long e = (long)blockIdx.x * 32 + lane;
+  // lanes past the last chain leave (2M is even, so re/im pairs stay complete for the shuffles of the wall
+  // correction); every warp of a block keeps at least one pair, so the block barriers below stay valid
+  if (e >= 2 * a.M) return;
+  const bool active = true;
+  setup_chain(a, e, md, wv);
+  const long st = 2 * a.M, M = a.M; const int ny = a.ny; const int c = md.c;
+  const T dt = (T)a.sc->dt;
+  const T s = wv.sc;
+  const int top = ny - 1;
+  const int sst = 32, pst = 16;
+  const long tile = (long)blockIdx.x * 32 * ny + lane;     // this block's warp tile of the scratch
+  double* const sA0 = a.sA + tile; double* const sB0 = a.sB + tile; double* const sC0 = a.sC + tile;
+  double* const sP0 = a.sP + (long)blockIdx.x * 16 * ny + (lane >> 1);
+  const T2* const H1 = a.ox + md.m; const T2* const H3 = a.oz + md.m; const T* const H2 = (const T*)a.oy + e;
+  T* const phi = (T*)a.phi + e; T* const g = (T*)a.g + e;
+  // P1
+  if (active) {
+    ElimD1P el;
+    if (role < 2) {
+      const T* const f = role == 0 ? phi : g; double* const sX = role == 0 ? sA0 : sB0;
+      sweep_rows<16>(ny, [&](int j) { return f[(long)j * st]; },
+                     [&](int j, const T& v) { el.step(a.yt.d1[0], j, ny, (double)v, sX + j * sst, sst); });
+    } else {
+      struct Row { T2 h1, h3; };
+      sweep_rows<8>(ny, [&](int j) { Row r; r.h1 = H1[(long)j * M]; r.h3 = H3[(long)j * M]; return r; },
+                    [&](int j, const Row& r) {
+                      T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
+                      T hv = -s * (wv.k1 * h1p + wv.k3 * h3p);
+                      el.step(a.yt.d1[0], j, ny, (double)hv, sC0 + j * sst, sst);
+                    });
+    }
+  }
+  __syncthreads();
+  // P2
+  if (active) {
+    double* const sX = role == 0 ? sA0 : (role == 1 ? sB0 : sC0);
+    ElimD1P el; double x = 0.0;
+    sweep_rows<16>(ny, [&](int jj) { return sX[(top - jj) * sst]; },
+                   [&](int jj, const double& d) {
+                     const int j = top - jj;
+                     x = d - __ldg(a.yt.d1[0].cp + j) * x;
+                     if (role == 2) sX[j * sst] = rnd<T>(x);
+                     else el.step(a.yt.d1[1], jj, ny, rnd<T>(x), sX + j * sst, -sst);
+                   });
+  }
+  __syncthreads();
+  // P3
+  const double bdt = (double)(dt * a.betha);
+  const double Dimp = a.nuD * bdt;
+  if (active && role < 2) {
+    ElimVarP<1> ev; double x = 0.0;
+    T* const R = (role == 0 ? (T*)a.Rphi : (T*)a.Rg) + e;
+    T* const f = role == 0 ? phi : g; double* const sX = role == 0 ? sA0 : sB0;
+    struct Row { double d, dC; T2 h1, h3; T h2, f, r; };
+    sweep_rows<6>(ny,
+      [&](int j) {
+        Row r; r.d = sX[j * sst]; r.f = f[(long)j * st]; r.r = R[(long)j * st];
+        if (role == 0) { r.dC = sC0[j * sst]; r.h2 = H2[(long)j * st]; r.h1 = mk0<T2>(); r.h3 = mk0<T2>(); }
+        else { r.h1 = H1[(long)j * M]; r.h3 = H3[(long)j * M]; r.dC = 0.0; r.h2 = 0; }
+        return r;
+      },
+      [&](int j, const Row& r) {
+        x = r.d - __ldg(a.yt.d1[1].cp + (top - j)) * x;
+        T fyy = (T)x, rnew;
+        if (role == 0) rnew = (T)r.dC - wv.kk * r.h2;                                   // calcHvvkernel (:180-181)
+        else { T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c); rnew = s * (wv.k3 * h1p - wv.k1 * h3p); }
+        T fw = r.f + dt * (a.alpha * a.nuT * (fyy - wv.kk * r.f) + a.dseda * r.r);
+        fw = fw + dt * a.gammad * rnew;
+        R[(long)j * st] = rnew;
+        const double ff[1] = { (double)fw };
+        double* const cur[1] = { sX + j * sst };
+        ev.step(a.yt.d2[0], j, ny, ff, true, wv.kkd, Dimp, cur, sst, sP0 + j * pst, pst);   // both roles write the same pivots
+      });
+  }
+  __syncthreads();
+  // P4
+  if (active && role < 2) {
+    ElimVarP<1> eh; double x = 0.0;
+    T* const f = role == 0 ? phi : g; double* const sX = role == 0 ? sA0 : sB0;
+    struct Row { double d, cp; };
+    sweep_rows<16>(ny, [&](int jj) { int j = top - jj; Row r; r.d = sX[j * sst]; r.cp = sP0[j * pst]; return r; },
+                   [&](int jj, const Row& r) {
+                     const int j = top - jj;
+                     x = r.d - r.cp * x;
+                     f[(long)j * st] = (T)x;
+                     if (role == 0) {
+                       const double ff[1] = { rnd<T>(x) };
+                       double* const cur[1] = { sX + j * sst };
+                       eh.step(a.yt.d2[1], jj, ny, ff, false, wv.kkd, 0.0, cur, -sst, sC0 + j * sst, -sst);
+                     }
+                   });
+  }
+  __syncthreads();
+  // P5, P6
+  if (active && role == 0) {
+    {
+      ElimD1P ev; double xv = 0.0;
+      T* const pv = (T*)a.v + e;
+      struct Row { double dA, cp; };
+      sweep_rows<16>(ny, [&](int j) { Row r; r.dA = sA0[j * sst]; r.cp = sC0[j * sst]; return r; },
+                     [&](int j, const Row& r) {
+                       xv = r.dA - r.cp * xv;
+                       pv[(long)j * st] = (T)xv;
+                       ev.step(a.yt.d1[0], j, ny, rnd<T>(xv), sA0 + j * sst, sst);
+                     });
+    }
+    double x = 0.0, dvm = 0.0, dvp = 0.0;
+    T* const pdv = (T*)a.dv + e;
+    sweep_rows<16>(ny, [&](int jj) { return sA0[(top - jj) * sst]; },
+                   [&](int jj, const double& dA) {
+                     const int j = top - jj;
+                     x = dA - __ldg(a.yt.d1[0].cp + j) * x;
+                     pdv[(long)j * st] = (T)x;
+                     if (j == top) dvp = rnd<T>(x);
+                     if (j == 0) dvm = rnd<T>(x);
+                   });
+    wall[0][lane] = dvm; wall[1][lane] = dvp;
+  }
+  __syncthreads();
+  // P7
+  if (active) bc_correct<T>(a, md, wv, a.betha, dt, (T*)a.phi, (T*)a.v, (T*)a.dv, wall[0][lane], wall[1][lane], role, 3);
+}
+
+// =================================================================================
 // generic operator kernel (operator-level C ABI and the RKstep prologue)
 // =================================================================================
 template <typename T>
@@ -592,7 +738,8 @@ static int post_t(chan_handle* h, int n) {
   long nchain = 2 * h->d.M;
   const int bt = h->tune.post_deep ? 32 : h->tune.post_threads;   // few chains: one warp per block, spread over all SMs
   const unsigned grid = (unsigned)((nchain + bt - 1) / bt);
-  if (h->tune.post_deep) pencil_post_kernel<T, true><<<grid, bt, 0, h->stream>>>(a);
+  if (h->tune.post_deep == 2) pencil_post_roles_kernel<T><<<(unsigned)((nchain + 31) / 32), 96, 0, h->stream>>>(a);
+  else if (h->tune.post_deep) pencil_post_kernel<T, true><<<grid, bt, 0, h->stream>>>(a);
   else pencil_post_kernel<T, false><<<grid, bt, 0, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());

@@ -36,9 +36,16 @@ template <typename T>
 struct Wave { T k1, k3, kk, rkk; double kkd; T sc; T sp; };   // rkk = 1/kk (1 for the mean mode)   // sc = sign of own component of i*z: -1 (re), +1 (im)
 
 template <typename T>
+__device__ __forceinline__ void setup_chain(const PArgs<T>& a, long e, Mode& md, Wave<T>& wv);
+template <typename T>
 __device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) {
   long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= 2 * a.M) return false;
+  setup_chain(a, e, md, wv);
+  return true;
+}
+template <typename T>
+__device__ __forceinline__ void setup_chain(const PArgs<T>& a, long e, Mode& md, Wave<T>& wv) {
   md.e = e; md.m = e >> 1; md.c = (int)(e & 1);
   int ikx = a.ikx0 + (int)(md.m / a.Kz);
   md.kzi = (int)(md.m % a.Kz);
@@ -52,7 +59,6 @@ __device__ __forceinline__ bool setup(const PArgs<T>& a, Mode& md, Wave<T>& wv) 
   wv.kkd = k1d * k1d + k3d * k3d;
   wv.sc = md.c ? (T)1 : (T)-1;
   wv.sp = -wv.sc;
-  return true;
 }
 
 __device__ __forceinline__ int phys_row(int dir, int jj, int ny) { return dir ? ny - 1 - jj : jj; }
