@@ -99,6 +99,57 @@ def test_rk3_steps_vs_reference_build(cg, case, sub, n, fixed, tol):
     ch.close()
 
 
+# The library picks its wall-normal kernels and launch shapes by how many chains a rank holds, so a multi-GPU run
+# mixes them across ranks.  The three thread-per-chain `post` kernels do the same arithmetic in the same order
+# (bit-identical), and so does any FFT launch shape; the segment-parallel register kernels compose affine maps
+# instead of sweeping sequentially (round-off level differences).  The knobs are read by chan_create from the
+# environment (channel_gpu_b200/csrc/api.cu).
+CHAIN = {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0"}
+SAME_BITS_AS_CHAIN = [
+    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "1"},      # deep-batch post
+    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "2"},      # three-role post
+    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0", "CHAN_TUNE_Z_THREADS": "256", "CHAN_TUNE_Z_XP": "2",
+     "CHAN_TUNE_X_THREADS": "256", "CHAN_TUNE_X_TK": "4"},          # other FFT launch shapes
+]
+ROUND_OFF_OF_CHAIN = [
+    {"CHAN_TUNE_PENCIL_SEG": "1", "CHAN_TUNE_POST_DEEP": "0"},      # register pre
+    {"CHAN_TUNE_PENCIL_SEG": "3"},                                  # register pre and post
+    {},                                                             # whatever the size heuristics pick
+]
+
+
+@pytest.mark.parametrize("case,sub,n,tol,eps", [("64x21x9_f64", "steps2", 2, 1e-11, 1e-13), ("192x19x13_f32", "steps2", 2, 1e-4, 2e-6)])
+def test_kernel_variants(cg, monkeypatch, case, sub, n, tol, eps):
+    g = Golden(case)
+    ddv, gg, um = g.inputs()
+    names = ("ddv", "g", "v", "dv", "R_ddv", "R_g")
+
+    def run(env):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        ch = cg.Channel(g.nx, g.ny, g.nz, precision=4 if g.prec == 32 else 8)
+        ch.RKstep(ddv, gg, n, fixed_dt=g.dt, umean=um)
+        out = {k: ch.get_field(k) for k in names}
+        out["umean"] = ch.get_umean()
+        ch.close()
+        for k in env:
+            monkeypatch.delenv(k)
+        return out
+
+    base = run(CHAIN)
+    for name in names:
+        assert rel(base[name], g.full(f"{sub}/{name}")) < tol, name
+    for env in SAME_BITS_AS_CHAIN:
+        got = run(env)
+        for name in list(names) + ["umean"]:
+            assert np.array_equal(got[name], base[name]), (env, name)
+    for env in ROUND_OFF_OF_CHAIN:
+        got = run(env)
+        for name in names:
+            assert rel(got[name], base[name]) < eps, (env, name)
+            assert rel(got[name], g.full(f"{sub}/{name}")) < tol, (env, name)
+
+
 def test_rk3_step_vs_oracle_re180(cg):
     """BASELINE.json configs[0] grid (128x97x65), fp64, two steps against the CPU oracle."""
     from bench import synthetic_fields
