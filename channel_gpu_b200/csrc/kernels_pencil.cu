@@ -238,6 +238,28 @@ __device__ void var_solve(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, 
 }
 
 // phi, v, dv: real views; dvm, dvp: own component of dv at j=0, NY-1 (state-type values)
+// Double-buffered variant: the loads of batch k+1 are issued before batch k is worked on, so a thread always has
+// U..2U rows of loads in flight (for passes whose rows are cheap in registers).  Legal wherever sweep_rows is:
+// a pass only ever writes rows it has already loaded.
+template <int U, class Load, class Proc>
+__device__ __forceinline__ void sweep_rows_db(int ny, Load ld, Proc pr) {
+  decltype(ld(0)) nx[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) nx[u] = ld(min(u, ny - 1));
+  for (int j0 = 0; j0 < ny; j0 += U) {
+    decltype(ld(0)) r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) r[u] = nx[u];
+    if (j0 + U < ny) {
+#pragma unroll
+      for (int u = 0; u < U; u++) nx[u] = ld(min(j0 + U + u, ny - 1));
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < U; u++) if (j0 + u < ny) pr(j0 + u, r[u]);
+  }
+}
+
 template <typename T>
 __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv, T betha, T dt,
                            T* phi, T* v, T* dv, double dvm, double dvp, int part = 0, int nparts = 1) {
@@ -252,9 +274,8 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
   double c2 = -p.dv1 * dvm + q.dv1 * dvp; c2 = -c2 / det;
   T* const pp = phi + md.e; T* const pv = v + md.e; T* const pd = dv + md.e;
   struct Row { T p, v, d; };
-  sweep_rows<8>(ny,
-    [&](int j) { Row r; r.p = pp[(long)j * st]; r.v = pv[(long)j * st]; r.d = pd[(long)j * st]; return r; },
-    [&](int j, const Row& r) {
+  auto ld = [&](int j) { Row r; r.p = pp[(long)j * st]; r.v = pv[(long)j * st]; r.d = pd[(long)j * st]; return r; };
+  auto pr = [&](int j, const Row& r) {
       BcFun f = bc_functions(k, __ldg(a.yt.y + j), md.c);
       double ppv = (double)r.p, vv = (double)r.v, dd = (double)r.d;
       ppv = ppv + c1 * f.ddv1 + c2 * f.ddv2;
@@ -262,7 +283,9 @@ __device__ void bc_correct(const PArgs<T>& a, const Mode& md, const Wave<T>& wv,
       vv = vv + c1 * f.v1 + c2 * f.v2;
       if (md.zero_mode) { ppv = 0.0; vv = 0.0; dd = 0.0; }
       pp[(long)j * st] = (T)ppv; pv[(long)j * st] = (T)vv; pd[(long)j * st] = (T)dd;
-    }, part, nparts);
+    };
+  if (nparts == 1) sweep_rows_db<4>(ny, ld, pr);
+  else sweep_rows<8>(ny, ld, pr, part, nparts);
 }
 
 // =================================================================================
@@ -356,6 +379,14 @@ __global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut 
 // DEEP = false: 128 registers, four blocks per SM (a GPU full of chains, bandwidth-bound).
 // DEEP = true: few chains per SM (many ranks, small grids): occupancy is irrelevant and a pass costs one
 // memory latency per batch, so the batches are as deep as 255 registers allow.
+#ifndef POST_DB
+#define POST_DB 1
+#endif
+#if POST_DB
+#define SWEEP_DB(U) sweep_rows_db<(U) / 2>
+#else
+#define SWEEP_DB(U) sweep_rows<U>
+#endif
 template <typename T, bool DEEP>
 __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T> a) {
   constexpr int PU1 = DEEP ? 8 : 6, PU2 = DEEP ? 12 : 8, PU3 = DEEP ? 6 : 3, PU4 = DEEP ? 12 : 8, PU5 = DEEP ? 16 : 8, PU6 = DEEP ? 16 : 8;
@@ -380,7 +411,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
   {
     ElimD1P ep, eg, eh;
     struct Row { T2 h1, h3; T p, g; };
-    sweep_rows<PU1>(ny,
+    SWEEP_DB(PU1)(ny,
       [&](int j) { Row r; r.h1 = H1[(long)j * M]; r.h3 = H3[(long)j * M]; r.p = phi[(long)j * st]; r.g = g[(long)j * st]; return r; },
       [&](int j, const Row& r) {
         T h1p = other<T2, T>(r.h1, c), h3p = other<T2, T>(r.h3, c);
@@ -396,7 +427,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
     ElimD1P ep, eg;
     double xp = 0.0, xg = 0.0, xh = 0.0;
     struct Row { double dA, dB, dC; };
-    sweep_rows<PU2>(ny,
+    SWEEP_DB(PU2)(ny,
       [&](int jj) { int j = top - jj; Row r; r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.dC = sC0[j * sst]; return r; },
       [&](int jj, const Row& r) {
         const int j = top - jj;
@@ -446,7 +477,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
     ElimVarP<1> eh;
     double xp = 0.0, xg = 0.0;
     struct Row { double dA, dB, cp; };
-    sweep_rows<PU4>(ny,
+    SWEEP_DB(PU4)(ny,
       [&](int jj) { int j = top - jj; Row r; r.dA = sA0[j * sst]; r.dB = sB0[j * sst]; r.cp = sP0[j * pst]; return r; },
       [&](int jj, const Row& r) {
         const int j = top - jj;
@@ -465,7 +496,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
     double xv = 0.0;
     T* const pv = (T*)a.v + e;
     struct Row { double dA, cp; };
-    sweep_rows<PU5>(ny,
+    SWEEP_DB(PU5)(ny,
       [&](int j) { Row r; r.dA = sA0[j * sst]; r.cp = sP0[j * pst]; return r; },
       [&](int j, const Row& r) {
         xv = r.dA - r.cp * xv;
