@@ -49,6 +49,8 @@ struct FftPlan {
   int span[16];                 // sub-transform size entering stage t (1, r0, r0*r1, ...)
   unsigned span_magic[16];      // FastDiv magic of span[t] (fft_core.cuh)
   int r_first, r_last;          // radix[0], radix[nstage-1]
+  unsigned rfirst_magic;        // FastDiv magic of r_first (row skew of the z transforms; 0 in PlanT.fsk.d turns it off)
+  int tws[16];                  // twiddle stride of stage t: n / (span[t] * radix[t])
   const void* tw;               // T2[n]: exp(-2 pi i k / n)
   const int* inv;               // digit-reversed position -> natural index
   const int* pos;               // natural index -> digit-reversed position

@@ -127,7 +127,6 @@ template <int R, int SIGN, class T2> FFT_HD void apply_twiddles(T2* a, const T2*
 // skew(row) = row / sk for sk > 0 (z transforms: one extra element every r_0 rows, so that rows that differ
 // in the HIGH digits of the digit-reversed position fall into different banks, see z_unpack_store), 0 for sk = 0.
 // sk divides the span m of every stage but the m = 1 stage, where all rows of a butterfly share one skew.
-FFT_HD int skew_of(int row, int sk, float rsk) { return sk ? (int)(((float)row + 0.5f) * rsk) : 0; }
 
 // Division of a work-item index by a launch-time constant.  The generic integer divisions of the index
 // arithmetic were ~15 % of the z kernel's instructions (ncu source view); with M = floor(2^32/d) + 1 the
@@ -143,19 +142,20 @@ FFT_HD int fd_div(int b, FastDiv f) {
 #endif
 }
 FFT_HD void fd_divmod(int b, FastDiv f, int& q, int& r) { q = fd_div(b, f); r = b - q * (int)f.d; }
+// skew(row) = row / r_0 for the z transforms (fsk = FastDiv of r_0), 0 for fsk.d = 0 (x transforms)
+FFT_HD int skew_of(int row, FastDiv fsk) { return fsk.d ? fd_div(row, fsk) : 0; }
 
 template <class T2, int R, int SIGN, bool DIT>
-FFT_HD void smem_stage(T2* s, int n, FastDiv fm, int st, FastDiv flines, int nact, int nper, const T2* tw, int tid, int nthr, int sk = 0) {
-  const int m = (int)fm.d, nlines = (int)flines.d;
-  const int nb = n / R, tws = nb / m;
-  const float rsk = sk ? 1.0f / (float)sk : 0.0f;
-  const int qst = m * st + ((sk && m >= sk) ? skew_of(m, sk, rsk) : 0);
+FFT_HD void smem_stage(T2* s, int n, FastDiv fm, int st, FastDiv flines, int nact, int nper, const T2* tw, int tid, int nthr, FastDiv fsk, int tws) {
+  const int m = (int)fm.d, nlines = (int)flines.d;     // tws = n / (m R), the twiddle stride of this stage
+  const int nb = n / R;
+  const int qst = m * st + ((fsk.d && m >= (int)fsk.d) ? skew_of(m, fsk) : 0);
   for (int b = tid; b < nb * nlines; b += nthr) {
     int l, bf; fd_divmod(b, flines, bf, l);
     int li = nact == nper ? l : (l / nact) * nper + l % nact;
     int g, k; fd_divmod(bf, fm, g, k);
     const int row0 = g * m * R + k;
-    T2* p = s + (size_t)row0 * st + skew_of(row0, sk, rsk) + li;
+    T2* p = s + (size_t)row0 * st + skew_of(row0, fsk) + li;
     T2 a[R];
 #pragma unroll
     for (int q = 0; q < R; q++) a[q] = p[(size_t)q * qst];

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
   if (a.dbg_stop == 1) return;
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.SS, a.f_lin, ST, ST, tid, nthr, pl.r_first); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr); __syncthreads(); }
   if (a.dbg_stop == 2) return;
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   }
   __syncthreads();
   if (MODE == ZM_ROTOR && tid < 3) atomicMax(a.umax_bits + tid, red[tid]);
-  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.SS, a.f_lout, NOUT, NOUT, tid, nthr, pl.r_first); __syncthreads(); }
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lout, NOUT, NOUT, tid, nthr); __syncthreads(); }
   if (a.dbg_stop == 4) return;
   z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SS, nxp_valid, tid, nthr);
 }

@@ -141,6 +141,8 @@ void make_plan(FftPlan* p, int n, bool small_last, int max_radix) {
   int span = 1;
   for (int i = 0; i < ns; i++) { p->radix[i] = best[i]; p->span[i] = span; p->span_magic[i] = fft::make_fastdiv(span).M; span *= best[i]; }
   p->r_first = ns ? p->radix[0] : 0; p->r_last = ns ? p->radix[ns - 1] : 0;
+  p->rfirst_magic = ns ? fft::make_fastdiv(p->radix[0]).M : 0;
+  for (int i = 0; i < ns; i++) p->tws[i] = n / (p->span[i] * p->radix[i]);
 }
 
 template <typename T>

@@ -21,10 +21,10 @@ namespace fft {
 
 // scalar view of an FftPlan: the radix/span arrays are read from the FftPlan itself (a kernel parameter,
 // i.e. constant bank) so that no per-thread local copy of them is made
-template <class T2> struct PlanT { int n, nstage, r_first, r_last; const T2* tw; const int* inv; const int* pos; };
+template <class T2> struct PlanT { int n, nstage, r_first, r_last; FastDiv fsk; const T2* tw; const int* inv; const int* pos; };   // fsk: FastDiv of r_first
 
 template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
-  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage; q.r_first = p.r_first; q.r_last = p.r_last;
+  PlanT<T2> q; q.n = p.n; q.nstage = p.nstage; q.r_first = p.r_first; q.r_last = p.r_last; q.fsk.d = (unsigned)p.r_first; q.fsk.M = p.rfirst_magic;
   q.tw = (const T2*)p.tw; q.inv = p.inv; q.pos = p.pos;
   return q;
 }
@@ -146,8 +146,8 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
 template <class T2, int SIGN, bool DIT>
-FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int sk = 0) {
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, sk)));
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr) {
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws)));
 }
 
 template <class T2, int SIGN, bool DIT, int TK>
@@ -235,16 +235,15 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
   typedef typename RealOf<T2>::type T;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
-  const int m = (int)fmid.d, sk = pl.r_first;            // m = n / R
-  const float rsk = 1.0f / (float)sk;
-  const int ist = m * SS + skew_of(m, sk, rsk);          // r_0 divides m = n / r_last (nstage >= 2)
+  const int m = (int)fmid.d;                             // m = n / R
+  const int ist = m * SS + skew_of(m, pl.fsk);           // r_0 divides m = n / r_last (nstage >= 2)
   const T rn2 = ((T)1 / n2) * ((T)1 / n2);
   const int nround = (m * XP + nthr - 1) / nthr;
   for (int it = 0; it < nround; it++) {
     const int b = tid + it * nthr;
     int k, xpl; fd_divmod(b, fmid, xpl, k);
     const bool work = b < m * XP && xpl < nxp_valid;
-    const size_t row = (size_t)k * SS + skew_of(k, sk, rsk);
+    const size_t row = (size_t)k * SS + skew_of(k, pl.fsk);
     T2 a[NIN][R];
     if (work) {
 #pragma unroll
@@ -304,15 +303,14 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
 template <class T2, int NIN, int NOUT>
 FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fkz, int XP, int SS, int nxp_valid, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
-  const int n = pl.n, sk = pl.r_first, Kz = (int)fkz.d;
-  const float rsk = 1.0f / (float)sk;
+  const int n = pl.n, Kz = (int)fkz.d;
   for (int b = tid; b < Kz * NOUT * XP; b += nthr) {
     int k, l; fd_divmod(b, fkz, l, k);
     const int xpl = l / NOUT, f = l - xpl * NOUT;
     if (xpl >= nxp_valid) continue;
     const int pk = FFT_LDG(pl.pos + k), pn = FFT_LDG(pl.pos + (k ? n - k : 0));
-    T2 Yk = s[(size_t)pk * SS + skew_of(pk, sk, rsk) + xpl * NOUT + f];
-    T2 Yn = s[(size_t)pn * SS + skew_of(pn, sk, rsk) + xpl * NOUT + f];
+    T2 Yk = s[(size_t)pk * SS + skew_of(pk, pl.fsk) + xpl * NOUT + f];
+    T2 Yn = s[(size_t)pn * SS + skew_of(pn, pl.fsk) + xpl * NOUT + f];
     const T h = (T)0.5;
     T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
     qa[k] = mk2<T2>(h * (Yk.x + Yn.x), h * (Yk.y - Yn.y));

@@ -104,7 +104,7 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   std::vector<T> phys((size_t)nxrows * (n + 2), (T)0);
   T um[3] = { 0, 0, 0 };
   EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, nxp_valid, Kz, tid, NTHR))); }
-  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), SS, make_fastdiv(ST), ST, ST, tid, NTHR, pl.r_first);
+  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR);
   EACH_THREAD {
     switch (pl.r_last) {
       case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
@@ -113,7 +113,7 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
     }
   }
   if (MODE != ZM_EXPORT) {
-    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), SS, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR, pl.r_first);
+    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR);
     EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, make_fastdiv(Kz), XP, SS, nxp_valid, tid, NTHR);
   }
   // reference
