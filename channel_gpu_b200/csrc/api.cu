@@ -214,7 +214,21 @@ static void* field_ptr(chan_handle* h, int which) {
 extern "C" int chan_set_field(chan_handle* h, int which, const void* host) {
   if (!h || !host) return CHAN_ERR_ARG;
   void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
-  CHAN_CUDA(h, cudaMemcpyAsync(h->io_buf, host, ref_bytes(h), cudaMemcpyHostToDevice, h->stream));
+  if (h->cfg.size == 1) {
+    CHAN_CUDA(h, cudaMemcpyAsync(h->io_buf, host, ref_bytes(h), cudaMemcpyHostToDevice, h->stream));
+  } else {
+    // a rank packs only the rows of its own kx slab: copy just those (at most two contiguous runs of i = kx or NX + kx)
+    const Dims& d = h->d;
+    const size_t row = (size_t)d.nz * d.ny * csize(h);
+    const int lo = d.ikx0, hi = d.ikx0 + d.Kxl;                 // active-kx indices [lo, hi)
+    const int p1 = hi < d.kxmax + 1 ? hi : d.kxmax + 1;         // kx >= 0 part: i = ikx
+    if (lo < p1) CHAN_CUDA(h, cudaMemcpyAsync((char*)h->io_buf + lo * row, (const char*)host + lo * row, (size_t)(p1 - lo) * row, cudaMemcpyHostToDevice, h->stream));
+    const int n0 = lo > d.kxmax + 1 ? lo : d.kxmax + 1;         // kx < 0 part: i = NX - Kx + ikx
+    if (n0 < hi) {
+      const size_t i0 = (size_t)(d.nx - d.Kx + n0);
+      CHAN_CUDA(h, cudaMemcpyAsync((char*)h->io_buf + i0 * row, (const char*)host + i0 * row, (size_t)(hi - n0) * row, cudaMemcpyHostToDevice, h->stream));
+    }
+  }
   int rc = launch_pack(h, h->io_buf, f); if (rc) return rc;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
