@@ -89,6 +89,7 @@ struct ZArgs {
   T2* Q; FftPlan pz;
   int dbg_stop;                    // >0: timing ablation only (CHAN_TUNE_Z_STOP): return after phase N
   int nx, nzp, Kz, pb, j_start, XP, SS;   // SS: shared-memory elements per position (>= XP*NIN)
+  int SSo, SKo;                    // forward-side row pitch and skew multiplier (plane_core.cuh)
   FastDiv f_lin, f_lout, f_ng, f_mid, f_kz;   // lines in / out, n/r_first, n/r_last, Kz (index arithmetic without divisions)
   T n2;                            // (T)N2: the reference divides by the int N2 (convolution_kernels.cu:107-121)
   unsigned long long* umax_bits;   // 3 slots
@@ -124,9 +125,9 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   T* phys = 0; size_t pxs = 0;
   if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
   switch (pl.r_last) {
-    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
   if (MODE == ZM_EXPORT) return;
   if (a.dbg_stop == 3) return;
@@ -144,9 +145,9 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   }
   __syncthreads();
   if (MODE == ZM_ROTOR && tid < 3) atomicMax(a.umax_bits + tid, red[tid]);
-  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lout, NOUT, NOUT, tid, nthr); __syncthreads(); }
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SSo, a.f_lout, NOUT, NOUT, tid, nthr, a.SKo); __syncthreads(); }
   if (a.dbg_stop == 4) return;
-  z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SS, nxp_valid, tid, nthr);
+  z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SSo, a.SKo, nxp_valid, tid, nthr);
 }
 
 // -------------------------------------------------------------------------------
@@ -211,6 +212,11 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   size_t sm = ((size_t)n * ss + n / h->pz.radix[0]) * sizeof(T2);      // rows + their skew (plane_core.cuh)
   if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
   a.XP = xp; a.SS = ss;
+  {
+    const int lout = xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1));
+    const bool pack = h->tune.z_fwdpack && (lout & 1) && m * xp <= threads && MODE == ZM_ROTOR;
+    a.SSo = pack ? lout : ss; a.SKo = pack ? lout : 1;
+  }
   a.f_lin = make_fastdiv(xp * nin); a.f_lout = make_fastdiv(xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1)));
   a.f_ng = make_fastdiv(n / h->pz.r_first); a.f_mid = make_fastdiv(m); a.f_kz = make_fastdiv(h->d.Kz);
   CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

@@ -146,8 +146,8 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
 template <class T2, int SIGN, bool DIT>
-FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr) {
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws)));
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int skm = 1) {
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws, skm)));
 }
 
 template <class T2, int SIGN, bool DIT, int TK>
@@ -160,6 +160,11 @@ FFT_HD void plan_stage_x(T2* s, const PlanT<T2>& pl, int r, int m, int tid, int 
 // >= XP*NIN; the pos/r_0 skew is explained at z_unpack_store).  Inverse side: slot = xpl*NIN + f.  Forward
 // side: slot = xpl*NOUT + f, i.e. the NOUT output lines of all x-pairs are packed next to each other so
 // that the forward stages touch contiguous elements (z_mid_fused makes the switch behind a barrier).
+// When the number L of forward lines is odd and the fused middle stage is a single round, the forward side
+// uses rows of exactly L elements with skew L*(pos/r_0): the shared stages then walk one contiguous
+// array (pitch SS left a hole per row that cost every second quarter-warp a bank conflict), L odd keeps
+// the lanes of the middle stage (consecutive rows) apart, and r_0*L + L = L (mod 8) keeps the groups of
+// the m = 1 stage apart.
 // Two-for-one: line (xpl, f) holds field f at x0 = 2*xp (real part) and x1 = 2*xp+1 (imaginary part).
 #ifdef __CUDA_ARCH__
 #define FFT_BLOCK_SYNC() __syncthreads()
@@ -230,13 +235,14 @@ enum { ZM_ROTOR = 0, ZM_IDENTITY = 1, ZM_EXPORT = 2 };
 // read in the same or an earlier round of the loop, so one barrier per round between the reads and the
 // writes is enough.  The host emulation (threads run one after the other) passes a separate s_out.
 template <class T2, int R, int MODE>
-FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv fmid, int XP, int SS, int nxp_valid, typename RealOf<T2>::type n2,
+FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv fmid, int XP, int SS, int SSo, int SKo, int nxp_valid, typename RealOf<T2>::type n2,
                         typename RealOf<T2>::type* umax3, typename RealOf<T2>::type* phys, size_t phys_xstride, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
   const int m = (int)fmid.d;                             // m = n / R
   const int ist = m * SS + skew_of(m, pl.fsk);           // r_0 divides m = n / r_last (nstage >= 2)
+  const int osto = m * SSo + SKo * skew_of(m, pl.fsk);   // forward-side rows: pitch SSo, skew multiplier SKo
   const T rn2 = ((T)1 / n2) * ((T)1 / n2);
   const int nround = (m * XP + nthr - 1) / nthr;
   for (int it = 0; it < nround; it++) {
@@ -244,6 +250,7 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
     int k, xpl; fd_divmod(b, fmid, xpl, k);
     const bool work = b < m * XP && xpl < nxp_valid;
     const size_t row = (size_t)k * SS + skew_of(k, pl.fsk);
+    const size_t rowo = (size_t)k * SSo + SKo * skew_of(k, pl.fsk);
     T2 a[NIN][R];
     if (work) {
 #pragma unroll
@@ -288,7 +295,7 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
 #pragma unroll
       for (int f = 0; f < NOUT; f++) {
 #pragma unroll
-        for (int i = 0; i < R; i++) s_out[row + (size_t)i * ist + xpl * NOUT + f] = a[f][i];
+        for (int i = 0; i < R; i++) s_out[rowo + (size_t)i * osto + xpl * NOUT + f] = a[f][i];
       }
     }
   }
@@ -301,7 +308,7 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
 // all fall into the same banks (7x the ideal number of wavefronts in the ncu source view).  The
 // pos/r_0 skew of the layout spreads exactly those rows over the banks.
 template <class T2, int NIN, int NOUT>
-FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fkz, int XP, int SS, int nxp_valid, int tid, int nthr) {
+FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fkz, int XP, int SS, int SK, int nxp_valid, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
   const int n = pl.n, Kz = (int)fkz.d;
   for (int b = tid; b < Kz * NOUT * XP; b += nthr) {
@@ -309,8 +316,8 @@ FFT_HD void z_unpack_store(const T2* s, T2* q0, size_t fstride, const PlanT<T2>&
     const int xpl = l / NOUT, f = l - xpl * NOUT;
     if (xpl >= nxp_valid) continue;
     const int pk = FFT_LDG(pl.pos + k), pn = FFT_LDG(pl.pos + (k ? n - k : 0));
-    T2 Yk = s[(size_t)pk * SS + skew_of(pk, pl.fsk) + xpl * NOUT + f];
-    T2 Yn = s[(size_t)pn * SS + skew_of(pn, pl.fsk) + xpl * NOUT + f];
+    T2 Yk = s[(size_t)pk * SS + SK * skew_of(pk, pl.fsk) + xpl * NOUT + f];
+    T2 Yn = s[(size_t)pn * SS + SK * skew_of(pn, pl.fsk) + xpl * NOUT + f];
     const T h = (T)0.5;
     T2* qa = q0 + f * fstride + (size_t)(2 * xpl) * Kz;
     qa[k] = mk2<T2>(h * (Yk.x + Yn.x), h * (Yk.y - Yn.y));

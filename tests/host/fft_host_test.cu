@@ -96,6 +96,9 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   Host<T2> H; H.build(n, true);
   PlanT<T2> pl = plan_of<T2>(H.p);
   int Kz = n / 3 + 1, nxrows = 2 * XP, ST = XP * NIN, SS = ST | 1;
+  // forward side: packed rows of L = XP*NOUT elements with skew multiplier L when L is odd (as launch_z chooses)
+  const int LO = XP * NOUT; const bool pack = (LO & 1) && MODE == ZM_ROTOR;
+  const int SSo = pack ? LO : SS, SKo = pack ? LO : 1;
   size_t fstride = (size_t)nxrows * Kz;
   std::vector<T2> Q((size_t)NIN * fstride), Q0, s((size_t)n * SS + n), s2((size_t)n * SS + n);
   for (auto& v : Q) { v.x = (T)frand(); v.y = (T)frand(); }
@@ -107,14 +110,14 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR);
   EACH_THREAD {
     switch (pl.r_last) {
-      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
     }
   }
   if (MODE != ZM_EXPORT) {
-    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR);
-    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, make_fastdiv(Kz), XP, SS, nxp_valid, tid, NTHR);
+    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SSo, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR, SKo);
+    EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, make_fastdiv(Kz), XP, SSo, SKo, nxp_valid, tid, NTHR);
   }
   // reference
   double err = 0, nrm = 0, umref[3] = { 0, 0, 0 };
