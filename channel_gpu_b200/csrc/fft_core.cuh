@@ -146,16 +146,17 @@ FFT_HD void fd_divmod(int b, FastDiv f, int& q, int& r) { q = fd_div(b, f); r = 
 FFT_HD int skew_of(int row, FastDiv fsk) { return fsk.d ? fd_div(row, fsk) : 0; }
 
 template <class T2, int R, int SIGN, bool DIT>
-FFT_HD void smem_stage(T2* s, int n, FastDiv fm, int st, FastDiv flines, int nact, int nper, const T2* tw, int tid, int nthr, FastDiv fsk, int tws, int skm = 1) {
-  const int m = (int)fm.d, nlines = (int)flines.d;     // tws = n / (m R), the twiddle stride of this stage; skm: skew multiplier
+FFT_HD void smem_stage(T2* s, int n, FastDiv fm, int st, FastDiv flines, int nact, int nper, const T2* tw, int tid, int nthr, FastDiv fsk, int tws, int skm = 1, int sha = -1) {
+  // tws = n / (m R), the twiddle stride of this stage; row address = row*st + skm*(row/r_0) + (row >> sha) [sha >= 0]
+  const int m = (int)fm.d, nlines = (int)flines.d;
   const int nb = n / R;
-  const int qst = m * st + ((fsk.d && m >= (int)fsk.d) ? skm * skew_of(m, fsk) : 0);
+  const int qst = m * st + ((fsk.d && m >= (int)fsk.d) ? skm * skew_of(m, fsk) + (sha >= 0 ? m >> sha : 0) : 0);
   for (int b = tid; b < nb * nlines; b += nthr) {
     int l, bf; fd_divmod(b, flines, bf, l);
     int li = nact == nper ? l : (l / nact) * nper + l % nact;
     int g, k; fd_divmod(bf, fm, g, k);
     const int row0 = g * m * R + k;
-    T2* p = s + (size_t)row0 * st + skm * skew_of(row0, fsk) + li;
+    T2* p = s + (size_t)row0 * st + skm * skew_of(row0, fsk) + (sha >= 0 ? row0 >> sha : 0) + li;
     T2 a[R];
 #pragma unroll
     for (int q = 0; q < R; q++) a[q] = p[(size_t)q * qst];

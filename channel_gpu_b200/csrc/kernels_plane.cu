@@ -90,6 +90,7 @@ struct ZArgs {
   int dbg_stop;                    // >0: timing ablation only (CHAN_TUNE_Z_STOP): return after phase N
   int nx, nzp, Kz, pb, j_start, XP, SS;   // SS: shared-memory elements per position (>= XP*NIN)
   int SSo, SKo;                    // forward-side row pitch and skew multiplier (plane_core.cuh)
+  int sha;                         // inverse-side extra skew row >> sha (-1: none, rows padded to an odd pitch instead)
   FastDiv f_lin, f_lout, f_ng, f_mid, f_kz;   // lines in / out, n/r_first, n/r_last, Kz (index arithmetic without divisions)
   T n2;                            // (T)N2: the reference divides by the int N2 (convolution_kernels.cu:107-121)
   unsigned long long* umax_bits;   // 3 slots
@@ -116,18 +117,18 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.pz);
   const size_t fstride = (size_t)a.pb * a.nx * a.Kz;
   T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
-  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, nxp_valid, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, a.sha, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
   if (a.dbg_stop == 1) return;
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr, 1, a.sha); __syncthreads(); }
   if (a.dbg_stop == 2) return;
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
   if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
   switch (pl.r_last) {
-    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
-    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 2: z_mid_fused<T2, 2, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.sha, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    case 3: z_mid_fused<T2, 3, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.sha, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
+    default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.sha, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
   if (MODE == ZM_EXPORT) return;
   if (a.dbg_stop == 3) return;
@@ -206,17 +207,22 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   // one thread per item of the register-fused middle stage (m positions x xp pairs), within 128..256
   int threads = h->tune.z_threads;
   if (threads <= 0) { threads = (m * xp + 31) / 32 * 32; threads = threads < 128 ? 128 : (threads > 256 ? 256 : threads); }
-  // an odd number of elements per position keeps the register-fused middle stage (threads stride
-  // over positions) free of bank conflicts
-  int ss = xp * nin; if (h->tune.z_pad && !(ss & 1)) ss++;
-  size_t sm = ((size_t)n * ss + n / h->pz.radix[0]) * sizeof(T2);      // rows + their skew (plane_core.cuh)
-  if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
-  a.XP = xp; a.SS = ss;
-  {
-    const int lout = xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1));
-    const bool pack = h->tune.z_fwdpack && (lout & 1) && m * xp <= threads && MODE == ZM_ROTOR;
-    a.SSo = pack ? lout : ss; a.SKo = pack ? lout : 1;
+  // Row layouts (plane_core.cuh).  Packed rows need the fused middle stage to be a single round (its barrier then
+  // separates ALL reads of the inverse side from the writes of the forward side, whatever the two layouts are).
+  const int nout = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1), lout = xp * nout;
+  const bool single = m * xp <= threads && MODE == ZM_ROTOR;
+  int ss = xp * nin, sha = -1;
+  if (!(ss & 1)) {
+    if (h->tune.z_inpack && single && m % 16 == 0) sha = (ss % 8 == 0) ? 0 : ((ss % 8 == 4) ? 1 : 2);   // the shifts divide every span
+    else if (h->tune.z_pad) ss++;            // an odd pitch keeps the lanes of the middle stage (consecutive rows) apart
   }
+  const bool pack = h->tune.z_fwdpack && (lout & 1) && single;
+  a.XP = xp; a.SS = ss; a.sha = sha;
+  a.SSo = pack ? lout : (ss | 1); a.SKo = pack ? lout : 1;
+  const size_t nsk = n / h->pz.radix[0];
+  const size_t ext_in = (size_t)n * ss + nsk + (sha >= 0 ? (n >> sha) : 0), ext_out = (size_t)n * a.SSo + a.SKo * nsk + lout;
+  size_t sm = (ext_in > ext_out ? ext_in : ext_out) * sizeof(T2);
+  if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
   a.f_lin = make_fastdiv(xp * nin); a.f_lout = make_fastdiv(xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1)));
   a.f_ng = make_fastdiv(n / h->pz.r_first); a.f_mid = make_fastdiv(m); a.f_kz = make_fastdiv(h->d.Kz);
   CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

@@ -146,8 +146,8 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
 template <class T2, int SIGN, bool DIT>
-FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int skm = 1) {
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws, skm)));
+FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int skm = 1, int sha = -1) {
+  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws, skm, sha)));
 }
 
 template <class T2, int SIGN, bool DIT, int TK>
@@ -160,6 +160,9 @@ FFT_HD void plan_stage_x(T2* s, const PlanT<T2>& pl, int r, int m, int tid, int 
 // >= XP*NIN; the pos/r_0 skew is explained at z_unpack_store).  Inverse side: slot = xpl*NIN + f.  Forward
 // side: slot = xpl*NOUT + f, i.e. the NOUT output lines of all x-pairs are packed next to each other so
 // that the forward stages touch contiguous elements (z_mid_fused makes the switch behind a barrier).
+// Inverse side with an even number L of lines (always: 6 per x-pair): rows of exactly L elements and an extra
+// skew row >> sha (sha = 2 for L = 2, 6 mod 8; 1 for 4; 0 for 0) instead of a one-element pad per row: the
+// shared stages cross a hole only every 2^sha rows, the lanes of the middle stage (consecutive rows) stay apart.
 // When the number L of forward lines is odd and the fused middle stage is a single round, the forward side
 // uses rows of exactly L elements with skew L*(pos/r_0): the shared stages then walk one contiguous
 // array (pitch SS left a hole per row that cost every second quarter-warp a bank conflict), L odd keeps
@@ -191,7 +194,7 @@ FFT_HD T2 z_packed_combine(T2 A, T2 B, int k, int kind) {
 // inverse, stage 0 fused with the packing load.  q0 -> Q[field 0][plane][x = 2*xp0][0]; fields are
 // fstride apart, x rows Kz apart.
 template <class T2, int R, int NIN>
-FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fng, int XP, int SS, int nxp_valid, int Kz, int tid, int nthr) {
+FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T2>& pl, FastDiv fng, int XP, int SS, int sha, int nxp_valid, int Kz, int tid, int nthr) {
   const int n = pl.n, ng = (int)fng.d, ST = XP * NIN;
   // lanes run over the groups g: for a fixed input q the natural indices inv[g*R] + q*ng of the ng groups
   // are a permutation of ng CONSECUTIVE kz, so a warp's load is one contiguous piece of a spectral row
@@ -222,7 +225,7 @@ FFT_HD void z_inv_load_stage0(T2* s, const T2* q0, size_t fstride, const PlanT<T
       for (int i = 0; i < R; i++) a[i] = mk2<T2>(0, 0);
     }
 #pragma unroll
-    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * SS + g + li] = a[p];     // skew(g*R + p) = g
+    for (int p = 0; p < R; p++) s[(size_t)(g * R + p) * SS + g + (sha >= 0 ? (g * R + p) >> sha : 0) + li] = a[p];     // (g*R + p) / r_0 = g
   }
 }
 
@@ -235,13 +238,13 @@ enum { ZM_ROTOR = 0, ZM_IDENTITY = 1, ZM_EXPORT = 2 };
 // read in the same or an earlier round of the loop, so one barrier per round between the reads and the
 // writes is enough.  The host emulation (threads run one after the other) passes a separate s_out.
 template <class T2, int R, int MODE>
-FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv fmid, int XP, int SS, int SSo, int SKo, int nxp_valid, typename RealOf<T2>::type n2,
+FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv fmid, int XP, int SS, int sha, int SSo, int SKo, int nxp_valid, typename RealOf<T2>::type n2,
                         typename RealOf<T2>::type* umax3, typename RealOf<T2>::type* phys, size_t phys_xstride, int tid, int nthr) {
   typedef typename RealOf<T2>::type T;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
   const int m = (int)fmid.d;                             // m = n / R
-  const int ist = m * SS + skew_of(m, pl.fsk);           // r_0 divides m = n / r_last (nstage >= 2)
+  const int ist = m * SS + skew_of(m, pl.fsk) + (sha >= 0 ? m >> sha : 0);   // r_0 (and 2^sha) divide m = n / r_last (nstage >= 2)
   const int osto = m * SSo + SKo * skew_of(m, pl.fsk);   // forward-side rows: pitch SSo, skew multiplier SKo
   const T rn2 = ((T)1 / n2) * ((T)1 / n2);
   const int nround = (m * XP + nthr - 1) / nthr;
@@ -249,7 +252,7 @@ FFT_HD void z_mid_fused(const T2* s_in, T2* s_out, const PlanT<T2>& pl, FastDiv 
     const int b = tid + it * nthr;
     int k, xpl; fd_divmod(b, fmid, xpl, k);
     const bool work = b < m * XP && xpl < nxp_valid;
-    const size_t row = (size_t)k * SS + skew_of(k, pl.fsk);
+    const size_t row = (size_t)k * SS + skew_of(k, pl.fsk) + (sha >= 0 ? k >> sha : 0);
     const size_t rowo = (size_t)k * SSo + SKo * skew_of(k, pl.fsk);
     T2 a[NIN][R];
     if (work) {

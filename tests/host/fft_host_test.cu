@@ -95,24 +95,26 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   constexpr int NOUT = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 0);
   Host<T2> H; H.build(n, true);
   PlanT<T2> pl = plan_of<T2>(H.p);
-  int Kz = n / 3 + 1, nxrows = 2 * XP, ST = XP * NIN, SS = ST | 1;
+  int Kz = n / 3 + 1, nxrows = 2 * XP, ST = XP * NIN, SS = ST | 1, sha = -1;
+  // inverse side as launch_z lays it out: packed rows + extra skew when the line count is even and 16 | n / r_last
+  if (MODE == ZM_ROTOR && !(ST & 1) && (n / pl.r_last) % 16 == 0) { SS = ST; sha = (ST % 8 == 0) ? 0 : ((ST % 8 == 4) ? 1 : 2); }
   // forward side: packed rows of L = XP*NOUT elements with skew multiplier L when L is odd (as launch_z chooses)
   const int LO = XP * NOUT; const bool pack = (LO & 1) && MODE == ZM_ROTOR;
-  const int SSo = pack ? LO : SS, SKo = pack ? LO : 1;
+  const int SSo = pack ? LO : (SS | 1), SKo = pack ? LO : 1;
   size_t fstride = (size_t)nxrows * Kz;
-  std::vector<T2> Q((size_t)NIN * fstride), Q0, s((size_t)n * SS + n), s2((size_t)n * SS + n);
+  std::vector<T2> Q((size_t)NIN * fstride), Q0, s((size_t)n * (SS + 2) + n), s2((size_t)n * (SS + 2) + n);
   for (auto& v : Q) { v.x = (T)frand(); v.y = (T)frand(); }
   Q0 = Q;
   T n2 = (T)7.0;
   std::vector<T> phys((size_t)nxrows * (n + 2), (T)0);
   T um[3] = { 0, 0, 0 };
-  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, nxp_valid, Kz, tid, NTHR))); }
-  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR);
+  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, sha, nxp_valid, Kz, tid, NTHR))); }
+  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR, 1, sha);
   EACH_THREAD {
     switch (pl.r_last) {
-      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
-      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, sha, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      case 3: z_mid_fused<T2, 3, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, sha, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
+      default: z_mid_fused<T2, 4, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, sha, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
     }
   }
   if (MODE != ZM_EXPORT) {
