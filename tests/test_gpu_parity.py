@@ -209,6 +209,33 @@ def test_wall_normal_sweep_vs_oracle_and_variants(cg, monkeypatch, ny):
         assert rel(regs[name], chain[name]) < (1e-10 if name == "R_ddv" else 1e-12), name
 
 
+@pytest.mark.parametrize("grid", [(48, 17, 385), (64, 17, 193), (32, 17, 65), (96, 17, 97), (48, 17, 49)])
+def test_z_row_layouts_bit_identical(cg, monkeypatch, grid):
+    """The shared-memory row layouts of the z stage (packed rows, skews: plane_core.cuh) change no arithmetic:
+    one RK3 step with them on and off, transform lengths 2NZ-2 = 768, 384, 128, 192, 96."""
+    from bench import synthetic_fields
+    nx, ny, nz = grid
+    ddv, gg, um = synthetic_fields(nx, ny, nz, np.complex128)
+    names = ("ddv", "g", "v", "dv", "R_ddv", "R_g")
+
+    def run(env):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        ch = cg.Channel(nx, ny, nz, precision=8)
+        ch.RKstep(ddv, gg, 1, fixed_dt=1e-3, umean=um)
+        out = {k: ch.get_field(k) for k in names}
+        ch.close()
+        for k in env:
+            monkeypatch.delenv(k)
+        return out
+
+    plain = run({"CHAN_TUNE_Z_INPACK": "0", "CHAN_TUNE_Z_FWDPACK": "0"})
+    packed = run({})
+    for name in names:
+        assert np.isfinite(packed[name]).all(), name
+        assert np.array_equal(packed[name], plain[name]), name
+
+
 def test_fused_substep_equals_operator_composition(cg):
     """The fused pencil kernels against the same substep assembled from the unfused
     operator-level entry points (an independent code path inside the library)."""
