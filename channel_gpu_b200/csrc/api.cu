@@ -143,7 +143,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // to fill the GPU with one thread per chain (small grids, many GPUs).
   // y stage: thread-per-chain kernels (batched row loads, HBM-bound) when there are enough chains to fill the
   // SMs, the segment-parallel register kernels when a rank holds few chains (many ranks / small grids)
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256) ? 1 : 0;     // `pre` only: the chain `post` wins at every size measured
+  // `pre`: the register kernel below 148*256 chains, and always when there are several GPUs - the thread-per-chain
+  // kernel walks the rows in order, so all ranks store into the SAME plane owner at the same time (measured at
+  // Re_tau=1000 on 8 GPUs: 3.1 ms per substep for 1/8 of the chains, as much as one GPU needs for all of them);
+  // the register kernel has every row in flight at once.
+  // `post`: the chain kernels win at every size measured.
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || cfg->size > 1) ? 1 : 0;
   if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));

@@ -1,7 +1,7 @@
 #!/bin/bash
 # z-stage launch shapes, Re550 fp64, one GPU: threads per block x x-pairs per block
 cd "$(dirname "$0")/.."
-for cfg in "0 0" "144 1" "160 1" "192 1"; do
+for cfg in "0 0" "256 2" "192 2" "96 1" "160 1"; do
   set -- $cfg
   echo -n "z_threads=$1 z_xp=$2 : "
   CHAN_TUNE_Z_THREADS=$1 CHAN_TUNE_Z_XP=$2 python bench.py --profile --steps 5 --warmup 2 2>&1 | tail -1 | python -c "
