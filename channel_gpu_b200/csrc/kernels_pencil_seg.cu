@@ -255,8 +255,8 @@ __device__ __forceinline__ bool setup_seg(const PArgs<T>& a, int cb, Mode& md, W
 }
 
 // =================================================================================
-template <typename T, int S, int CB, int MINB>
-__global__ void __launch_bounds__(CB * 32, MINB) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st, PeerOut po) {
+template <typename T, int S, int CB, int MINB, int LB>
+__global__ void __launch_bounds__(LB, MINB) pencil_pre_seg_kernel(PArgs<T> a, SegTabs st, PeerOut po) {
   typedef typename Vec2<T>::type T2;
   extern __shared__ double sm_seg[];
   Mode md; Wave<T> wv; Ctx c;
@@ -312,8 +312,8 @@ __global__ void __launch_bounds__(CB * 32, MINB) pencil_pre_seg_kernel(PArgs<T> 
 }
 
 // =================================================================================
-template <typename T, int S, int CB, int MINB>
-__global__ void __launch_bounds__(CB * 32, MINB) pencil_post_seg_kernel(PArgs<T> a, SegTabs st) {
+template <typename T, int S, int CB, int MINB, int LB>
+__global__ void __launch_bounds__(LB, MINB) pencil_post_seg_kernel(PArgs<T> a, SegTabs st) {
   typedef typename Vec2<T>::type T2;
   extern __shared__ double sm_seg[];
   Mode md; Wave<T> wv; Ctx c;
@@ -459,7 +459,9 @@ __global__ void __launch_bounds__(128) pivot_kernel(PArgs<T> a, double* __restri
 }
 
 // ---------------------------------------------------------------------------------
-static int seg_len(int ny) { return ny <= 256 ? 8 : (ny <= 512 ? 16 : (ny <= 768 ? 24 : 0)); }
+// rows per segment: 8 up to NY = 512 (up to 64 segments of 8 chains per block above NY = 256), 12 up to 768.  The
+// 16- and 24-row builds spill (ptxas: 1.4 KB per thread) and stay reachable through CHAN_TUNE_SEG_SHAPE only.
+static int seg_len(int ny) { return ny <= 512 ? 8 : (ny <= 768 ? 12 : 0); }
 int seg_supported(chan_handle* h) { return seg_len(h->d.ny) != 0 && h->d.ny >= 16; }
 
 int seg_setup(chan_handle* h) {
@@ -485,7 +487,8 @@ int seg_setup(chan_handle* h) {
   return CHAN_OK;
 }
 
-template <typename T, int S, int CB, int MINB = 1>
+// LB: launch bound = CB x the largest segment count the shape is used for
+template <typename T, int S, int CB, int MINB = 1, int LB = CB * 32>
 static int launch_seg(chan_handle* h, bool post, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   static const float kAlpha[3] = { 29.0f / 96.0f, -3.0f / 40.0f, 1.0f / 6.0f }, kDseda[3] = { 0.0f, -17.0f / 60.0f, -5.0f / 12.0f };
@@ -493,6 +496,7 @@ static int launch_seg(chan_handle* h, bool post, int n) {
   a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
   SegTabs st; st.pf = h->seg_pf; st.pb = h->seg_pb; st.pivH = h->pivH; st.pivI = h->pivI;
   const int nseg = (h->d.ny + S - 1) / S;
+  if (CB * nseg > LB) return set_err(h, CHAN_ERR_ARG, "segment shape %dx%d does not fit NY=%d", S, CB, h->d.ny);
   const long nchain = 2 * h->d.M;
   dim3 block(CB, nseg), grid((unsigned)((nchain + CB - 1) / CB));
   size_t sm = sizeof(double) * ((size_t)14 * nseg * CB + 2 * CB);
@@ -500,12 +504,12 @@ static int launch_seg(chan_handle* h, bool post, int n) {
     unsigned pg = (unsigned)((h->d.M + 127) / 128);
     if (!h->pivH_ready) { pivot_kernel<T><<<pg, 128, 0, h->stream>>>(a, h->pivH, 0); h->launches++; h->pivH_ready = 1; }
     pivot_kernel<T><<<pg, 128, 0, h->stream>>>(a, h->pivI, 1); h->launches++;
-    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_post_seg_kernel<T, S, CB, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    pencil_post_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st);
+    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_post_seg_kernel<T, S, CB, MINB, LB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    pencil_post_seg_kernel<T, S, CB, MINB, LB><<<grid, block, sm, h->stream>>>(a, st);
   } else {
-    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_seg_kernel<T, S, CB, MINB, LB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     PeerOut po; fill_peer_out(h, po);
-    pencil_pre_seg_kernel<T, S, CB, MINB><<<grid, block, sm, h->stream>>>(a, st, po);
+    pencil_pre_seg_kernel<T, S, CB, MINB, LB><<<grid, block, sm, h->stream>>>(a, st, po);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
@@ -521,14 +525,13 @@ static int launch_seg_any(chan_handle* h, bool post, int n) {
       case 808: return launch_seg<T, 8, 8, 2>(h, post, n);
       case 809: return launch_seg<T, 8, 8, 3>(h, post, n);
       case 804: return launch_seg<T, 8, 4, 4>(h, post, n);
+      case 1616: return launch_seg<T, 16, 16>(h, post, n);
+      case 2408: return launch_seg<T, 24, 8>(h, post, n);
       default: break;
     }
   }
-  switch (h->seg_S) {
-    case 8: return launch_seg<T, 8, 16>(h, post, n);
-    case 16: return launch_seg<T, 16, 16>(h, post, n);
-    default: return launch_seg<T, 24, 8>(h, post, n);
-  }
+  if (h->seg_S == 8) return h->d.ny <= 256 ? launch_seg<T, 8, 16>(h, post, n) : launch_seg<T, 8, 8, 1, 512>(h, post, n);
+  return launch_seg<T, 12, 8, 1, 512>(h, post, n);
 }
 int launch_pencil_pre_seg(chan_handle* h) { return h->prec == 4 ? launch_seg_any<float>(h, false, 0) : launch_seg_any<double>(h, false, 0); }
 int launch_pencil_post_seg(chan_handle* h, int n) { return h->prec == 4 ? launch_seg_any<float>(h, true, n) : launch_seg_any<double>(h, true, n); }

@@ -175,7 +175,7 @@ def test_rk3_step_vs_oracle_re180(cg):
 def test_wall_normal_sweep_vs_oracle_and_variants(cg, monkeypatch, ny):
     """BASELINE.json configs[4] (kernel sweep over NY): one RK3 step on a thin 24 x NY x 13 grid, fp64.  The
     thread-per-chain kernels against the CPU oracle (same tolerances as the Re_tau=180 case: the expf gap), and the
-    kernels the size heuristics pick (register `pre` with 8-, 16- or 24-row segments, three-role `post`) against
+    kernels the size heuristics pick (register `pre` with 8- or 12-row segments, three-role `post`) against
     the thread-per-chain ones to round-off."""
     from bench import synthetic_fields
     nx, nz = 24, 13
