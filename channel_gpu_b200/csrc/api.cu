@@ -73,7 +73,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
     struct { const char* name; int* v; int def; } knobs[] = {
       { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 0 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 0 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 0 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 }, { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1 }, { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1 } };
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 0 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 0 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 }, { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1 }, { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1 }, { "CHAN_TUNE_PRE_SCATTER", &h->tune.pre_scatter, 0 } };
     for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
   }
   Dims& d = h->d;

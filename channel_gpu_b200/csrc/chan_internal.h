@@ -123,7 +123,7 @@ struct chan_handle {
   chan::SegMap seg;               // plane-side segmentation (identical for every field)
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_scatter; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)

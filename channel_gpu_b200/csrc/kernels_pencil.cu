@@ -373,6 +373,23 @@ __global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut 
   }
 }
 
+// delivery of the six plane-stage inputs of row j (u, v, w, omega) to the rank that owns plane j; one thread per
+// complex element, every row in flight at once so that the stores spread over all destinations
+template <typename T>
+__global__ void __launch_bounds__(256) peer_scatter_kernel(PArgs<T> a, PeerOut po) {
+  typedef typename Vec2<T>::type T2;
+  const long m = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (m >= a.M) return;
+  int p = 0;
+#pragma unroll
+  for (int i = 1; i < 8; i++) p += (i < po.nranks && j >= po.part_j[i]) ? 1 : 0;
+  const long src = (long)j * a.M + m, dst = po.src_off[p] + (long)(j - po.part_j[p]) * a.M + m;
+  const T2* f[6] = { a.u, a.v, a.w, a.ox, a.oy, a.oz };
+#pragma unroll
+  for (int q = 0; q < 6; q++) ((T2*)po.rcv[p][q])[dst] = f[q][src];
+}
+
 // =================================================================================
 // pencil_post: H1..3, phi, g, R_phi, R_g -> phi, g, v, dv, R_phi, R_g   (7 passes)
 // =================================================================================
@@ -757,6 +774,18 @@ static int pre_t(chan_handle* h) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   long nchain = 2 * h->d.M;
   PeerOut po; fill_peer_out(h, po);
+  if (po.nranks > 1 && h->tune.pre_scatter) {
+    // experiment (CHAN_TUNE_PRE_SCATTER=1 with CHAN_TUNE_PENCIL_SEG=0): the chain kernel walks the rows in order, so
+    // its peer stores hit one plane owner at a time ("Incast"); store locally instead and let a
+    // kernel with every row in flight deliver the six fields
+    PeerOut local; memset(&local, 0, sizeof(local)); local.nranks = 1;
+    pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, local);
+    dim3 grid((unsigned)((h->d.M + 255) / 256), (unsigned)h->d.ny);
+    peer_scatter_kernel<T><<<grid, 256, 0, h->stream>>>(a, po);
+    h->launches += 2;
+    CHAN_CUDA(h, cudaGetLastError());
+    return CHAN_OK;
+  }
   pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, po);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
