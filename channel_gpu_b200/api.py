@@ -30,7 +30,7 @@ class _Config(C.Structure):
 
 class _Scalars(C.Structure):
     _fields_ = [("dt", C.c_double), ("dt_next", C.c_double), ("dt_c", C.c_double), ("dt_v", C.c_double),
-                ("umax", C.c_double * 3), ("utau", C.c_double * 2), ("counter", C.c_int)]
+                ("umax", C.c_double * 3), ("utau", C.c_double * 2), ("counter", C.c_int), ("time", C.c_double)]
 
 
 def lib_path():
@@ -53,6 +53,10 @@ def load_library():
         "chan_create": [C.POINTER(_Config), C.POINTER(vp)],
         "chan_set_fields": [vp, vp, vp], "chan_get_fields": [vp, vp, vp],
         "chan_get_field": [vp, ci, vp], "chan_set_field": [vp, ci, vp],
+        "chan_get_field_slab": [vp, ci, vp], "chan_set_field_slab": [vp, ci, vp],
+        "chan_get_field_dev": [vp, ci, vp], "chan_set_field_dev": [vp, ci, vp],
+        "chan_get_fields_dev": [vp, vp, vp], "chan_set_fields_dev": [vp, vp, vp],
+        "chan_checkpoint_save": [vp, vp], "chan_checkpoint_load": [vp, vp],
         "chan_set_umean": [vp, vp], "chan_get_umean": [vp, vp], "chan_get_nmean": [vp, vp],
         "chan_get_scalars": [vp, C.POINTER(_Scalars)],
         "chan_set_fixed_dt": [vp, cd], "chan_set_dt": [vp, cd],
@@ -77,6 +81,7 @@ def load_library():
     L.chan_destroy.argtypes = [vp]; L.chan_destroy.restype = None
     L.chan_last_error.argtypes = [vp]; L.chan_last_error.restype = C.c_char_p
     L.chan_launch_count.argtypes = [vp]; L.chan_launch_count.restype = C.c_long
+    L.chan_checkpoint_bytes.argtypes = [vp]; L.chan_checkpoint_bytes.restype = C.c_size_t
     _LIB = L
     return L
 
@@ -151,8 +156,8 @@ class Channel:
 
     def get_field(self, name, out=None):
         """`out`: optional destination (e.g. a view of pinned memory) of the reference shape and dtype."""
-        if out is None:
-            out = np.empty((self.nx, self.nz, self.ny), self.cplx)
+        if out is None:      # several ranks: a rank fills only the rows of its own kx slab
+            out = (np.empty if self.size == 1 else np.zeros)((self.nx, self.nz, self.ny), self.cplx)
         elif out.shape != (self.nx, self.nz, self.ny) or out.dtype != self.cplx or not out.flags["C_CONTIGUOUS"]:
             raise ChannelError("out must be a C-contiguous %s array of shape %s" % (np.dtype(self.cplx), (self.nx, self.nz, self.ny)))
         self._ck(self.L.chan_get_field(self.h, FIELDS[name], out.ctypes.data), "chan_get_field")
@@ -161,6 +166,39 @@ class Channel:
     def set_field(self, name, a):
         a = self._host(a)
         self._ck(self.L.chan_set_field(self.h, FIELDS[name], a.ctypes.data), "chan_set_field")
+
+    def slab(self):
+        """(first active-kx index, count) of this rank's pencil-stage slab and the reference row i of each slab row."""
+        Kx = 2 * (self.nx // 3) + 1
+        s0, c0 = partition(Kx, self.size, self.rank)
+        ikx = np.arange(s0, s0 + c0); kx = np.where(ikx <= self.nx // 3, ikx, ikx - Kx)
+        return s0, c0, np.where(kx >= 0, kx, kx + self.nx)
+
+    def set_field_slab(self, name, a):
+        """`a`: this rank's slab [Kxl][NZ][NY] in active-kx order (see slab())."""
+        a = np.ascontiguousarray(a, dtype=self.cplx)
+        if a.shape != (self.slab()[1], self.nz, self.ny):
+            raise ChannelError("expected slab shape %s, got %s" % ((self.slab()[1], self.nz, self.ny), a.shape))
+        self._ck(self.L.chan_set_field_slab(self.h, FIELDS[name], a.ctypes.data), "chan_set_field_slab")
+
+    def get_field_slab(self, name, out=None):
+        shp = (self.slab()[1], self.nz, self.ny)
+        if out is None:
+            out = np.empty(shp, self.cplx)
+        elif out.shape != shp or out.dtype != self.cplx or not out.flags["C_CONTIGUOUS"]:
+            raise ChannelError("out must be a C-contiguous %s array of shape %s" % (np.dtype(self.cplx), shp))
+        self._ck(self.L.chan_get_field_slab(self.h, FIELDS[name], out.ctypes.data), "chan_get_field_slab")
+        return out
+
+    def checkpoint_save(self):
+        """One rank's complete state as bytes (chan_checkpoint_save)."""
+        buf = np.empty(int(self.L.chan_checkpoint_bytes(self.h)), np.uint8)
+        self._ck(self.L.chan_checkpoint_save(self.h, buf.ctypes.data), "chan_checkpoint_save")
+        return buf
+
+    def checkpoint_load(self, buf):
+        buf = np.ascontiguousarray(buf, dtype=np.uint8)
+        self._ck(self.L.chan_checkpoint_load(self.h, buf.ctypes.data), "chan_checkpoint_load")
 
     def get_fields(self, out=None):
         """D2H + writeData payload (io.c:37-72).  `out`: optional (ddv, g) destination arrays."""
@@ -184,7 +222,7 @@ class Channel:
     def scalars(self):
         s = _Scalars()
         self._ck(self.L.chan_get_scalars(self.h, C.byref(s)), "chan_get_scalars")
-        return dict(dt=s.dt, dt_next=s.dt_next, dt_c=s.dt_c, dt_v=s.dt_v, umax=tuple(s.umax), utau=tuple(s.utau), counter=s.counter)
+        return dict(dt=s.dt, dt_next=s.dt_next, dt_c=s.dt_c, dt_v=s.dt_v, umax=tuple(s.umax), utau=tuple(s.utau), counter=s.counter, time=s.time)
 
     def set_fixed_dt(self, dt):
         self._ck(self.L.chan_set_fixed_dt(self.h, float(dt)), "chan_set_fixed_dt")

@@ -1,5 +1,6 @@
 """Builds channel_gpu_b200/lib/libchannel_b200.so from csrc/*.cu with nvcc for
 sm_100a (in-tree, so the .so travels to the GPU box with the repo snapshot)."""
+import glob
 import os
 import subprocess
 import sys
@@ -13,6 +14,10 @@ SOURCES = ["api.cu", "kernels_tables.cu", "kernels_pencil.cu", "kernels_pencil_s
 NVCC = os.environ.get("NVCC", "nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC"]
+# CHAN_ABLATE=1 python -m channel_gpu_b200.build --force : a build whose kernels honour the timing-ablation
+# knobs (CHAN_TUNE_*_STOP / CHAN_TUNE_X_SKIP, scripts/ablate_post.sh).  Never the shipped library.
+if os.environ.get("CHAN_ABLATE") == "1":
+    FLAGS.append("-DCHAN_ABLATE")
 
 
 def _stale(target, deps):
@@ -26,7 +31,7 @@ def build_lib(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    headers = [os.path.join(CSRC, h) for h in ("chan_internal.h", "fft_core.cuh", "plane_core.cuh", "fft_twiddle_consts.h")] + [os.path.join(HERE, "..", "include", "channel_b200.h")]
+    headers = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh"))) + [os.path.join(HERE, "..", "include", "channel_b200.h")]
     jobs = []
     objs = []
     for s in SOURCES:

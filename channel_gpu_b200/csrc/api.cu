@@ -11,7 +11,6 @@ using namespace chan;
 
 static size_t csize(const chan_handle* h) { return 2 * (size_t)h->prec; }                      // bytes per complex
 static size_t field_bytes(const chan_handle* h) { return (size_t)h->d.ny * h->d.M * csize(h); } // compact field
-static size_t ref_bytes(const chan_handle* h) { return (size_t)h->d.nx * h->d.nz * h->d.ny * csize(h); }
 
 extern "C" int chan_partition(int n, int size, int rank, int* start, int* count) {
   if (size <= 0 || rank < 0 || rank >= size || n < 0) return CHAN_ERR_ARG;
@@ -70,11 +69,35 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (cfg->size > 1 && !cfg->nccl_comm) return set_err(h, CHAN_ERR_ARG, "size > 1 needs chan_config.nccl_comm");
   h->nccl_comm = cfg->nccl_comm;
   h->prec = cfg->precision;
-  {   // launch shapes of the plane kernels; CHAN_TUNE_* environment variables override (used by scripts/sweep_plane.py)
-    struct { const char* name; int* v; int def; } knobs[] = {
-      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 0 }, { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0 }, { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1 },
-      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 0 }, { "CHAN_TUNE_X_TK", &h->tune.x_tk, 0 }, { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16 }, { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0 }, { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0 }, { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1 }, { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0 }, { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0 }, { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128 }, { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0 }, { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1 }, { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1 }, { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1 }, { "CHAN_TUNE_PRE_SCATTER", &h->tune.pre_scatter, 0 } };
-    for (auto& k : knobs) { const char* e = getenv(k.name); *k.v = e ? atoi(e) : k.def; }
+  {   // launch shapes and kernel choices; CHAN_TUNE_* environment variables override (scripts/sweep_*.sh, tests)
+    struct { const char* name; int* v; int def; bool ablate; } knobs[] = {
+      { "CHAN_TUNE_Z_THREADS", &h->tune.z_threads, 0, false },
+      { "CHAN_TUNE_Z_XP", &h->tune.z_xp, 0, false },
+      { "CHAN_TUNE_Z_PAD", &h->tune.z_pad, 1, false },
+      { "CHAN_TUNE_X_THREADS", &h->tune.x_threads, 0, false },
+      { "CHAN_TUNE_X_TK", &h->tune.x_tk, 0, false },
+      { "CHAN_TUNE_MAX_RADIX", &h->tune.max_radix, 16, false },
+      { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1, false },
+      { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0, false },
+      { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0, false },
+      { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128, false },
+      { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1, false },
+      { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1, false },
+      { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1, false },
+      { "CHAN_TUNE_PRE_SCATTER", &h->tune.pre_scatter, 0, false },
+      { "CHAN_TUNE_LANES", &h->tune.lanes, -1, false },
+      // timing ablation: kernels return early (results are garbage) - only in -DCHAN_ABLATE builds
+      { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0, true },
+      { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0, true },
+      { "CHAN_TUNE_POST_STOP", &h->tune.post_stop, 0, true } };
+    for (auto& k : knobs) {
+      const char* e = getenv(k.name);
+      *k.v = e ? atoi(e) : k.def;
+#ifndef CHAN_ABLATE
+      if (k.ablate && e && atoi(e) != 0)
+        return set_err(h, CHAN_ERR_ARG, "%s is set but this library was built without -DCHAN_ABLATE: it would make kernels return early", k.name);
+#endif
+    }
   }
   Dims& d = h->d;
   d.nx = cfg->nx; d.ny = cfg->ny; d.nz = cfg->nz; d.nzp = 2 * cfg->nz - 2;
@@ -134,8 +157,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if ((rc = alloc_dev(h, &h->mean_uw, rb))) return rc;
   if ((rc = alloc_dev(h, &h->mean_tmp, 6 * rb))) return rc;
   if ((rc = alloc_dev(h, (void**)&h->sc, sizeof(Scalars)))) return rc;
-  h->io_bytes = ref_bytes(h);
+  h->io_bytes = (size_t)d.Kxl * d.nz * d.ny * csize(h);              // the rank's slab of the reference layout
   if ((rc = alloc_dev(h, &h->io_buf, h->io_bytes))) return rc;
+  if ((rc = alloc_dev(h, (void**)&h->stat_buf, sizeof(double) * 4 * d.ny))) return rc;
   if ((rc = build_tables(h))) return rc;
   // wall-normal stage: bit 0 = segment-parallel pre kernel, bit 1 = segment-parallel post kernel.
   // Measured on B200 (profiles/): the register version of `pre` always wins; `post` is instruction-
@@ -164,7 +188,7 @@ extern "C" void chan_destroy(chan_handle* h) {
   }
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
                    h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
-                   h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
+                   h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->stat_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
@@ -216,33 +240,42 @@ static void* field_ptr(chan_handle* h, int which) {
   return (which >= 0 && which < CHAN_F_COUNT) ? t[which] : 0;
 }
 
+// The rank's active-kx slab [ikx0, ikx0+Kxl) is at most two runs of rows i of the reference array: kx >= 0 (i = kx)
+// and kx < 0 (i = NX + kx).  run r covers slab rows [s0, s0+n) = reference rows [i0, i0+n).
+struct IoRun { int s0, i0, n; };
+static int io_runs(const chan_handle* h, IoRun* r) {
+  const Dims& d = h->d;
+  const int lo = d.ikx0, hi = d.ikx0 + d.Kxl;
+  int nr = 0;
+  const int p1 = hi < d.kxmax + 1 ? hi : d.kxmax + 1;
+  if (lo < p1) { r[nr].s0 = 0; r[nr].i0 = lo; r[nr].n = p1 - lo; nr++; }
+  const int n0 = lo > d.kxmax + 1 ? lo : d.kxmax + 1;
+  if (n0 < hi) { r[nr].s0 = n0 - lo; r[nr].i0 = d.nx - d.Kx + n0; r[nr].n = hi - n0; nr++; }
+  return nr;
+}
+static size_t io_row_bytes(const chan_handle* h) { return (size_t)h->d.nz * h->d.ny * csize(h); }
+
 extern "C" int chan_set_field(chan_handle* h, int which, const void* host) {
   if (!h || !host) return CHAN_ERR_ARG;
   void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
-  if (h->cfg.size == 1) {
-    CHAN_CUDA(h, cudaMemcpyAsync(h->io_buf, host, ref_bytes(h), cudaMemcpyHostToDevice, h->stream));
-  } else {
-    // a rank packs only the rows of its own kx slab: copy just those (at most two contiguous runs of i = kx or NX + kx)
-    const Dims& d = h->d;
-    const size_t row = (size_t)d.nz * d.ny * csize(h);
-    const int lo = d.ikx0, hi = d.ikx0 + d.Kxl;                 // active-kx indices [lo, hi)
-    const int p1 = hi < d.kxmax + 1 ? hi : d.kxmax + 1;         // kx >= 0 part: i = ikx
-    if (lo < p1) CHAN_CUDA(h, cudaMemcpyAsync((char*)h->io_buf + lo * row, (const char*)host + lo * row, (size_t)(p1 - lo) * row, cudaMemcpyHostToDevice, h->stream));
-    const int n0 = lo > d.kxmax + 1 ? lo : d.kxmax + 1;         // kx < 0 part: i = NX - Kx + ikx
-    if (n0 < hi) {
-      const size_t i0 = (size_t)(d.nx - d.Kx + n0);
-      CHAN_CUDA(h, cudaMemcpyAsync((char*)h->io_buf + i0 * row, (const char*)host + i0 * row, (size_t)(hi - n0) * row, cudaMemcpyHostToDevice, h->stream));
-    }
-  }
-  int rc = launch_pack(h, h->io_buf, f); if (rc) return rc;
+  // a rank reads only the rows of its own kx slab out of the caller's full array
+  IoRun r[2]; const int nr = io_runs(h, r); const size_t row = io_row_bytes(h);
+  for (int q = 0; q < nr; q++)
+    CHAN_CUDA(h, cudaMemcpyAsync((char*)h->io_buf + r[q].s0 * row, (const char*)host + r[q].i0 * row, (size_t)r[q].n * row, cudaMemcpyHostToDevice, h->stream));
+  int rc = launch_pack(h, h->io_buf, f, 1); if (rc) return rc;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
 }
 extern "C" int chan_get_field(chan_handle* h, int which, void* host) {
   if (!h || !host) return CHAN_ERR_ARG;
   void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
-  int rc = launch_unpack(h, f, h->io_buf); if (rc) return rc;
-  CHAN_CUDA(h, cudaMemcpyAsync(host, h->io_buf, ref_bytes(h), cudaMemcpyDeviceToHost, h->stream));
+  int rc = launch_unpack(h, f, h->io_buf, 1); if (rc) return rc;
+  // a rank writes only the rows of its own kx slab into the caller's full array; rank 0 also clears the rows of the
+  // truncated kx (kxmax < kx < NX - kxmax), which belong to nobody's slab
+  IoRun r[2]; const int nr = io_runs(h, r); const size_t row = io_row_bytes(h);
+  for (int q = 0; q < nr; q++)
+    CHAN_CUDA(h, cudaMemcpyAsync((char*)host + r[q].i0 * row, (const char*)h->io_buf + r[q].s0 * row, (size_t)r[q].n * row, cudaMemcpyDeviceToHost, h->stream));
+  if (h->cfg.rank == 0) memset((char*)host + (size_t)(h->d.kxmax + 1) * row, 0, (size_t)(h->d.nx - h->d.Kx) * row);
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
 }
@@ -253,6 +286,92 @@ extern "C" int chan_set_fields(chan_handle* h, const void* ddv, const void* g) {
 extern "C" int chan_get_fields(chan_handle* h, void* ddv, void* g) {
   int rc = chan_get_field(h, CHAN_F_DDV, ddv); if (rc) return rc;
   return chan_get_field(h, CHAN_F_G, g);
+}
+// slab variants: host array [Kxl][NZ][NY], rows in active-kx order ikx0 .. ikx0+Kxl-1 (chan_partition(chan_active_kx(NX), size, rank))
+extern "C" int chan_set_field_slab(chan_handle* h, int which, const void* host_slab) {
+  if (!h || !host_slab) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  CHAN_CUDA(h, cudaMemcpyAsync(h->io_buf, host_slab, h->io_bytes, cudaMemcpyHostToDevice, h->stream));
+  int rc = launch_pack(h, h->io_buf, f, 1); if (rc) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_get_field_slab(chan_handle* h, int which, void* host_slab) {
+  if (!h || !host_slab) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  int rc = launch_unpack(h, f, h->io_buf, 1); if (rc) return rc;
+  CHAN_CUDA(h, cudaMemcpyAsync(host_slab, h->io_buf, h->io_bytes, cudaMemcpyDeviceToHost, h->stream));
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+// device variants: the caller's full reference-layout DEVICE arrays, no host staging (the coarse RKstep seam)
+extern "C" int chan_set_field_dev(chan_handle* h, int which, const void* dev) {
+  if (!h || !dev) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  int rc = launch_pack(h, dev, f, 0); if (rc) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_get_field_dev(chan_handle* h, int which, void* dev) {
+  if (!h || !dev) return CHAN_ERR_ARG;
+  void* f = field_ptr(h, which); if (!f) return set_err(h, CHAN_ERR_ARG, "bad field selector %d", which);
+  if (h->cfg.size > 1) return set_err(h, CHAN_ERR_STATE, "chan_get_field_dev clears the whole array: single-GPU handles only");
+  int rc = launch_unpack(h, f, dev, 0); if (rc) return rc;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
+}
+extern "C" int chan_set_fields_dev(chan_handle* h, const void* ddv, const void* g) {
+  int rc = chan_set_field_dev(h, CHAN_F_DDV, ddv); if (rc) return rc;
+  return chan_set_field_dev(h, CHAN_F_G, g);
+}
+extern "C" int chan_get_fields_dev(chan_handle* h, void* ddv, void* g) {
+  int rc = chan_get_field_dev(h, CHAN_F_DDV, ddv); if (rc) return rc;
+  return chan_get_field_dev(h, CHAN_F_G, g);
+}
+
+// ---- checkpoint / restart (no counterpart in the reference, which restarts from its end-of-run field files and
+// loses R_phi, R_g, dt: main.c:139, RK3.c:114) ------------------------------------------------------------
+// Payload of one rank: header | Scalars | host_counter | mean_u, mean_N (T[NY]) | phi g v dv R_phi R_g (compact slabs)
+struct CkptHeader { char magic[8]; int version, prec, nx, ny, nz, rank, size, ikx0, Kxl, Kz; long M; size_t bytes; };
+static const char kCkptMagic[8] = { 'C', 'H', 'B', '2', 'C', 'K', 'P', 'T' };
+static size_t ckpt_bytes(const chan_handle* h) {
+  return sizeof(CkptHeader) + sizeof(Scalars) + sizeof(long) + 2 * (size_t)h->d.ny * h->prec + 6 * field_bytes(h);
+}
+extern "C" size_t chan_checkpoint_bytes(const chan_handle* h) { return h ? ckpt_bytes(h) : 0; }
+extern "C" int chan_checkpoint_save(chan_handle* h, void* host_buf) {
+  if (!h || !host_buf) return CHAN_ERR_ARG;
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  char* p = (char*)host_buf;
+  CkptHeader hd; memset(&hd, 0, sizeof(hd));
+  memcpy(hd.magic, kCkptMagic, 8); hd.version = 1; hd.prec = h->prec; hd.nx = h->d.nx; hd.ny = h->d.ny; hd.nz = h->d.nz;
+  hd.rank = h->cfg.rank; hd.size = h->cfg.size; hd.ikx0 = h->d.ikx0; hd.Kxl = h->d.Kxl; hd.Kz = h->d.Kz; hd.M = h->d.M; hd.bytes = ckpt_bytes(h);
+  memcpy(p, &hd, sizeof(hd)); p += sizeof(hd);
+  CHAN_CUDA(h, cudaMemcpy(p, h->sc, sizeof(Scalars), cudaMemcpyDeviceToHost)); p += sizeof(Scalars);
+  memcpy(p, &h->host_counter, sizeof(long)); p += sizeof(long);
+  const size_t rb = (size_t)h->d.ny * h->prec, fb = field_bytes(h);
+  CHAN_CUDA(h, cudaMemcpy(p, h->mean_u, rb, cudaMemcpyDeviceToHost)); p += rb;
+  CHAN_CUDA(h, cudaMemcpy(p, h->mean_N, rb, cudaMemcpyDeviceToHost)); p += rb;
+  void* fl[6] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg };
+  for (int i = 0; i < 6; i++) { CHAN_CUDA(h, cudaMemcpy(p, fl[i], fb, cudaMemcpyDeviceToHost)); p += fb; }
+  return CHAN_OK;
+}
+extern "C" int chan_checkpoint_load(chan_handle* h, const void* host_buf) {
+  if (!h || !host_buf) return CHAN_ERR_ARG;
+  const char* p = (const char*)host_buf;
+  CkptHeader hd; memcpy(&hd, p, sizeof(hd)); p += sizeof(hd);
+  if (memcmp(hd.magic, kCkptMagic, 8) || hd.version != 1) return set_err(h, CHAN_ERR_ARG, "not a version-1 checkpoint");
+  if (hd.prec != h->prec || hd.nx != h->d.nx || hd.ny != h->d.ny || hd.nz != h->d.nz || hd.rank != h->cfg.rank || hd.size != h->cfg.size ||
+      hd.ikx0 != h->d.ikx0 || hd.Kxl != h->d.Kxl || hd.bytes != ckpt_bytes(h))
+    return set_err(h, CHAN_ERR_ARG, "checkpoint of grid %dx%dx%d precision %d rank %d/%d does not match this handle", hd.nx, hd.ny, hd.nz, hd.prec, hd.rank, hd.size);
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  CHAN_CUDA(h, cudaMemcpy(h->sc, p, sizeof(Scalars), cudaMemcpyHostToDevice)); p += sizeof(Scalars);
+  memcpy(&h->host_counter, p, sizeof(long)); p += sizeof(long);
+  const size_t rb = (size_t)h->d.ny * h->prec, fb = field_bytes(h);
+  CHAN_CUDA(h, cudaMemcpy(h->mean_u, p, rb, cudaMemcpyHostToDevice)); p += rb;
+  CHAN_CUDA(h, cudaMemcpy(h->mean_N, p, rb, cudaMemcpyHostToDevice)); p += rb;
+  void* fl[6] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg };
+  for (int i = 0; i < 6; i++) { CHAN_CUDA(h, cudaMemcpy(fl[i], p, fb, cudaMemcpyHostToDevice)); p += fb; }
+  return CHAN_OK;
 }
 
 extern "C" int chan_set_umean(chan_handle* h, const void* um) {
@@ -295,7 +414,7 @@ extern "C" int chan_get_scalars(chan_handle* h, chan_scalars* out) {
   out->dt = s.dt; out->dt_next = s.dt_next; out->dt_c = s.dt_c; out->dt_v = s.dt_v;
   for (int c = 0; c < 3; c++) out->umax[c] = s.umax[c];
   out->utau[0] = s.utau[0]; out->utau[1] = s.utau[1];
-  out->counter = s.counter;
+  out->counter = s.counter; out->time = s.time;
   return CHAN_OK;
 }
 static int poke_scalar(chan_handle* h, size_t off, double v) {
@@ -397,14 +516,13 @@ extern "C" int chan_rk_step(chan_handle* h, int nsteps) {
 
 extern "C" int chan_statistics(chan_handle* h, double* out) {
   if (!h || !out) return CHAN_ERR_ARG;
-  double* d; const size_t b = sizeof(double) * 4 * h->d.ny;
-  CHAN_CUDA(h, cudaMalloc(&d, b));
+  double* d = h->stat_buf; const size_t b = sizeof(double) * 4 * h->d.ny;
   int rc = launch_stats(h, d);
   if (!rc) rc = allreduce_sum_host(h, d, 4 * h->d.ny);
-  if (!rc) { cudaError_t e = cudaMemcpyAsync(out, d, b, cudaMemcpyDeviceToHost, h->stream); if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    if (e != cudaSuccess) rc = set_err(h, CHAN_ERR_CUDA, "statistics copy: %s", cudaGetErrorString(e)); }
-  cudaFree(d);
-  return rc;
+  if (rc) return rc;
+  CHAN_CUDA(h, cudaMemcpyAsync(out, d, b, cudaMemcpyDeviceToHost, h->stream));
+  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
+  return CHAN_OK;
 }
 
 // ---- operator level: device pointers, reference layout, in place ----------------------
@@ -460,7 +578,7 @@ extern "C" int chan_convolution(chan_handle* h, void* ux, void* uy, void* uz, vo
   if ((rc = launch_pack(h, uy, h->v))) return rc;
   if ((rc = launch_pack(h, uz, h->w))) return rc;
   if ((rc = launch_op(h, OP_OMEGA, 0, 0, 0, 0, 0))) return rc;            // d/dy u, d/dy w, omega
-  if ((rc = launch_nonlinear_planes(h))) return rc;
+  if ((rc = launch_nonlinear_planes(h, true))) return rc;
   CHAN_CUDA(h, cudaMemcpyAsync(h->v, h->sC, fb, cudaMemcpyDeviceToDevice, h->stream));
   if ((rc = launch_unpack(h, h->ox, wx))) return rc;
   if ((rc = launch_unpack(h, h->oy, wy))) return rc;

@@ -85,6 +85,8 @@ struct Scalars {                // device-resident step scalars (doubles hold T-
   double dudy_wall[2];          // d<u>/dy at j=0, NY-1 (convolution.c:14-16)
   double utau[2];
   int    counter;
+  double time;                  // sum of the dt of the steps taken (the reference ignores its `time` argument, RK3.c:126)
+  unsigned long long umax_scratch[3];   // sink of the maxima of operator-level launches (chan_convolution): they must not feed calcDt
 };
 
 }  // namespace chan
@@ -122,14 +124,24 @@ struct chan_handle {
   int part_kx[9], part_j[9];      // part_kx[r] = first active-kx index of rank r (part_kx[size] = Kx), same for planes
   chan::SegMap seg;               // plane-side segmentation (identical for every field)
   // boundary staging (reference layout <-> compact)
-  void* io_buf; size_t io_bytes;
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_scatter; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  void* io_buf; size_t io_bytes;   // the rank's slab [Kxl][NZ][NY] of the reference layout
+  double* stat_buf;             // 4*NY sums of chan_statistics
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_scatter, lanes; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
   int timing; int n_ev; cudaEvent_t ev0[1024], ev1[1024]; int ev_stage[1024];
   char err[256];
 };
+
+// Timing-ablation early returns (scripts/ablate_post.sh, CHAN_TUNE_*_STOP / CHAN_TUNE_X_SKIP) exist only in builds made
+// with -DCHAN_ABLATE; the shipped library has none, and chan_create refuses those variables so that a stray setting
+// cannot silently turn a run into a no-op.
+#ifdef CHAN_ABLATE
+#define CHAN_ABLATE_RETURN(cond) do { if (cond) return; } while (0)
+#else
+#define CHAN_ABLATE_RETURN(cond) do { } while (0)
+#endif
 
 namespace chan {
 enum { OP_DERIV_Y = 1, OP_DERIV_YY, OP_HELM, OP_IMPLICIT, OP_BILAP, OP_VDV, OP_UW, OP_HVG, OP_OMEGA };
@@ -153,12 +165,13 @@ int seg_setup(chan_handle* h);
 int launch_pencil_pre_seg(chan_handle* h);
 int launch_pencil_post_seg(chan_handle* h, int n);
 // kernels_plane.cu
-int launch_nonlinear_planes(chan_handle* h);                 // u,v,w,omega -> H (in ox,oy,oz)
+int launch_nonlinear_planes(chan_handle* h, bool op_level = false);   // u,v,w,omega -> H (in ox,oy,oz); op_level: inputs sit in the local pencil fields, step scalars untouched
 int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields
 int launch_to_physical(chan_handle* h, const void* f, void* phys_out);   // debug/parity: one field -> real [NY][NX][nzp]
 // kernels_misc.cu
-int launch_pack(chan_handle* h, const void* ref_layout_dev, void* compact);      // [i][k][j] -> [j][m]
-int launch_unpack(chan_handle* h, const void* compact, void* ref_layout_dev);    // [j][m] -> [i][k][j] (zeros outside)
+// slab = 0: the dense side is a full reference-layout array; 1: the rank's slab [Kxl][NZ][NY] in active-kx order
+int launch_pack(chan_handle* h, const void* ref_layout_dev, void* compact, int slab = 0);      // [i][k][j] -> [j][m]
+int launch_unpack(chan_handle* h, const void* compact, void* ref_layout_dev, int slab = 0);    // [j][m] -> [i][k][j] (zeros on truncated modes)
 int launch_scalar_stage(chan_handle* h, int n);              // mean flow, dt, bookkeeping
 int launch_end_step(chan_handle* h);
 // comm.cu

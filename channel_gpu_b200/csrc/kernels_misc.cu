@@ -9,14 +9,16 @@ namespace chan {
 //   <-> compact plane-major [j][ikx*Kz+kz] (kz fastest, active modes only).
 // A tiled transpose through shared memory, coalesced on both sides.
 // -------------------------------------------------------------------------------
+// slab = 1: the dense side is the rank's own slab [Kxl][NZ][NY] in active-kx order (the library's boundary staging
+// buffer); slab = 0: the caller's full reference-layout array [NX][NZ][NY].
 template <typename T2, bool PACK>
 __global__ void relayout_kernel(const T2* __restrict__ src, T2* __restrict__ dst, int nx, int ny, int nz,
-                                int Kx, int Kz, int kxmax, int ikx0, int Kxl) {
+                                int Kx, int Kz, int kxmax, int ikx0, int Kxl, int slab) {
   __shared__ T2 tile[32][33];
   const int ikxl = blockIdx.z;                 // local active kx
   const int ikx = ikx0 + ikxl;
   const int kx = ikx <= kxmax ? ikx : ikx - Kx;
-  const int i = kx >= 0 ? kx : kx + nx;
+  const int i = slab ? ikxl : (kx >= 0 ? kx : kx + nx);
   const int j0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
   const long M = (long)Kxl * Kz;
   if (PACK) {
@@ -43,21 +45,22 @@ __global__ void relayout_kernel(const T2* __restrict__ src, T2* __restrict__ dst
 }
 
 template <typename T>
-static int relayout_t(chan_handle* h, const void* src, void* dst, bool pack) {
+static int relayout_t(chan_handle* h, const void* src, void* dst, bool pack, int slab) {
   typedef typename Vec2<T>::type T2;
   const Dims& d = h->d;
   dim3 grid((d.ny + 31) / 32, (d.Kz + 31) / 32, d.Kxl), block(32, 8);
-  if (pack) relayout_kernel<T2, true><<<grid, block, 0, h->stream>>>((const T2*)src, (T2*)dst, d.nx, d.ny, d.nz, d.Kx, d.Kz, d.kxmax, d.ikx0, d.Kxl);
+  if (pack) relayout_kernel<T2, true><<<grid, block, 0, h->stream>>>((const T2*)src, (T2*)dst, d.nx, d.ny, d.nz, d.Kx, d.Kz, d.kxmax, d.ikx0, d.Kxl, slab);
   else {
-    CHAN_CUDA(h, cudaMemsetAsync(dst, 0, (size_t)d.nx * d.nz * d.ny * sizeof(T2), h->stream));
-    relayout_kernel<T2, false><<<grid, block, 0, h->stream>>>((const T2*)src, (T2*)dst, d.nx, d.ny, d.nz, d.Kx, d.Kz, d.kxmax, d.ikx0, d.Kxl);
+    // truncated modes come back as exact zeros (dealias.cu:37): clear the dense side first
+    CHAN_CUDA(h, cudaMemsetAsync(dst, 0, (size_t)(slab ? d.Kxl : d.nx) * d.nz * d.ny * sizeof(T2), h->stream));
+    relayout_kernel<T2, false><<<grid, block, 0, h->stream>>>((const T2*)src, (T2*)dst, d.nx, d.ny, d.nz, d.Kx, d.Kz, d.kxmax, d.ikx0, d.Kxl, slab);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
 }
-int launch_pack(chan_handle* h, const void* s, void* c) { return h->prec == 4 ? relayout_t<float>(h, s, c, true) : relayout_t<double>(h, s, c, true); }
-int launch_unpack(chan_handle* h, const void* c, void* s) { return h->prec == 4 ? relayout_t<float>(h, c, s, false) : relayout_t<double>(h, c, s, false); }
+int launch_pack(chan_handle* h, const void* s, void* c, int slab) { return h->prec == 4 ? relayout_t<float>(h, s, c, true, slab) : relayout_t<double>(h, s, c, true, slab); }
+int launch_unpack(chan_handle* h, const void* c, void* s, int slab) { return h->prec == 4 ? relayout_t<float>(h, c, s, false, slab) : relayout_t<double>(h, c, s, false, slab); }
 
 // -------------------------------------------------------------------------------
 // Scalar stage, once per substep after the plane stage: the (kx,kz)=(0,0) mean-flow
@@ -228,6 +231,7 @@ int launch_scalar_stage(chan_handle* h, int n) { return h->prec == 4 ? scalar_t<
 
 // RK3.c:179-180: dt lags one step; maxima restart for the next step's calcDt
 __global__ void end_step_kernel(Scalars* sc) {
+  sc->time += sc->dt;
   sc->dt = sc->dt_next;
   sc->counter += 1;
   sc->umax_bits[0] = sc->umax_bits[1] = sc->umax_bits[2] = 0ull;

@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut 
         ew.step(a.yt.d1[0], j, ny, (double)w, sB0 + j * sst, sst);
       });
   }
-  if (a.dbg_stop == 7) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 7);
   // pass 2 (down): back-substitute, build omega (calcOmegakernel, convolution_kernels.cu:46-53)
   {
     double xu = 0.0, xw = 0.0;
@@ -438,7 +438,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         eh.step(a.yt.d1[0], j, ny, (double)hv, sC0 + j * sst, sst);
       });
   }
-  if (a.dbg_stop == 1) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 1);
   // P2 (down): phi', g', hv' ; eliminate d/dy of phi', g' (second derivative = d/dy twice, Q4)
   {
     ElimD1P ep, eg;
@@ -455,7 +455,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         eg.step(a.yt.d1[1], jj, ny, rnd<T>(xg), sB0 + j * sst, -sst);
       });
   }
-  if (a.dbg_stop == 2) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 2);
   // P3 (up): phi'', g'' -> explicit RK update (rk_step_1/2, RK3_kernels.cu:76-80,138-142) -> eliminate implicit solves
   const double bdt = (double)(dt * a.betha);                         // dt*betha in the state type (:235)
   const double Dimp = a.nuD * bdt;
@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         ev.step(a.yt.d2[0], j, ny, f, true, wv.kkd, Dimp, cur, sst, sP0 + j * pst, pst);
       });
   }
-  if (a.dbg_stop == 3) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 3);
   // P4 (down): phi_new, g_new ; eliminate Helmholtz (D2 - kk) v = phi_new.  The Helmholtz elimination
   // lags one row ABOVE the row being read, so the batch of rows below still holds the implicit-solve data.
   {
@@ -506,7 +506,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         eh.step(a.yt.d2[1], jj, ny, f, false, wv.kkd, 0.0, cur, -sst, sP0 + j * pst, -pst);
       });
   }
-  if (a.dbg_stop == 4) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 4);
   // P5 (up): v ; eliminate d/dy v
   {
     ElimD1P ev;
@@ -521,7 +521,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         ev.step(a.yt.d1[0], j, ny, rnd<T>(xv), sA0 + j * sst, sst);
       });
   }
-  if (a.dbg_stop == 5) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 5);
   // P6 (down): dv
   double dvm = 0.0, dvp = 0.0;
   {
@@ -537,7 +537,7 @@ __global__ void __launch_bounds__(128, DEEP ? 1 : 4) pencil_post_kernel(PArgs<T>
         if (j == 0) dvm = rnd<T>(x);
       });
   }
-  if (a.dbg_stop == 6) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 6);
   // P7: wall correction (skipped when dt <= 1e-8, including the zeroing of mode (0,0))
   bc_correct<T>(a, md, wv, a.betha, dt, (T*)a.phi, (T*)a.v, (T*)a.dv, dvm, dvp);
 }
@@ -812,7 +812,7 @@ static int op_t(chan_handle* h, int op, void* f0, void* f1, void* f2, double bet
   a.op = op; a.f0 = (T2*)f0; a.f1 = (T2*)f1; a.f2 = (T2*)f2; a.op_betha = (T)betha; a.op_dt = (T)dt;
   long nchain = 2 * h->d.M;
   unsigned grid = (unsigned)((nchain + 127) / 128);
-  if (op == OP_OMEGA) { a.use_mean = 0; PeerOut po; memset(&po, 0, sizeof(po)); po.nranks = 1; pencil_pre_kernel<T><<<grid, 128, 0, h->stream>>>(a, po); }
+  if (op == OP_OMEGA) { a.use_mean = 0; a.sc = 0; PeerOut po; memset(&po, 0, sizeof(po)); po.nranks = 1; pencil_pre_kernel<T><<<grid, 128, 0, h->stream>>>(a, po); }
   else op_kernel<T><<<grid, 128, 0, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   T2* s = (T2*)smem_raw;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int kz0 = blockIdx.x * TK, jb = blockIdx.y, f = blockIdx.z;
-  if (a.dbg_skip & 1) return;
+  CHAN_ABLATE_RETURN(a.dbg_skip & 1);
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* src = a.src[f];
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   T2* s = (T2*)smem_raw;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int kz0 = blockIdx.x * TK, jb = blockIdx.y, f = blockIdx.z;
-  if (a.dbg_skip & 2) return;
+  CHAN_ABLATE_RETURN(a.dbg_skip & 2);
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
   FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   if (threadIdx.x < 3) red[threadIdx.x] = 0ull;          // barriers follow before its use
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int xp0 = blockIdx.x * a.XP, jb = blockIdx.y;
-  if (a.dbg_stop == 9) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 9);
   const int nxp_valid = min(a.XP, a.nx / 2 - xp0);
   const int ST = a.XP * NIN;
   const PlanT<T2> pl = plan_of<T2>(a.pz);
@@ -119,9 +119,9 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
   FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, a.sha, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
-  if (a.dbg_stop == 1) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 1);
   for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr, 1, a.sha); __syncthreads(); }
-  if (a.dbg_stop == 2) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 2);
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
   if (MODE == ZM_EXPORT) { pxs = (size_t)2 * a.nz; phys = a.phys + ((size_t)(a.j_glob0 + a.j_start + jb) * a.nx + 2 * xp0) * pxs; }
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
     default: z_mid_fused<T2, 4, MODE>(s, s, pl, a.f_mid, a.XP, a.SS, a.sha, a.SSo, a.SKo, nxp_valid, a.n2, um, phys, pxs, tid, nthr); break;
   }
   if (MODE == ZM_EXPORT) return;
-  if (a.dbg_stop == 3) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 3);
   if (MODE == ZM_ROTOR) {      // block max -> one atomic per block and component
     // values are >= 0, so the bit pattern orders like the value: warp maximum of the high words, then of
     // the low words among the lanes that hold it (two redux instead of ten 64-bit shuffle steps)
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   __syncthreads();
   if (MODE == ZM_ROTOR && tid < 3) atomicMax(a.umax_bits + tid, red[tid]);
   for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SSo, a.f_lout, NOUT, NOUT, tid, nthr, a.SKo); __syncthreads(); }
-  if (a.dbg_stop == 4) return;
+  CHAN_ABLATE_RETURN(a.dbg_stop == 4);
   z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SSo, a.SKo, nxp_valid, tid, nthr);
 }
 
@@ -260,18 +260,21 @@ static void peer_out(chan_handle* h, XArgs<T>& xf) {
 }
 
 template <typename T>
-static int nonlinear_t(chan_handle* h) {
+static int nonlinear_t(chan_handle* h, bool op_level) {
   typedef typename Vec2<T>::type T2;
   XArgs<T> xi, xf; fill_x(h, xi); fill_x(h, xf);
   void* pin[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
   void* pout[3] = { h->ox, h->oy, h->oz };
   const bool multi = h->cfg.size > 1, peer = multi && h->peer_ready;
-  if (peer) { int rc = stream_barrier(h); if (rc) return rc; }                 // every rank's `pre` has delivered
+  // operator-level calls (chan_convolution) left their inputs in the LOCAL pencil fields: nothing has been
+  // delivered to the plane owners, so the input side goes through the NCCL exchange even when peer stores are on
+  if (peer && !op_level) { int rc = stream_barrier(h); if (rc) return rc; }    // every rank's `pre` has delivered
   else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
   for (int f = 0; f < 6; f++) xi.src[f] = (const T2*)(multi ? h->rcv[f] : pin[f]);
   for (int f = 0; f < 3; f++) for (int g = 0; g < 8; g++) xf.dst[f].p[g] = (T2*)(multi ? h->snd[f] : pout[f]);
   if (peer) peer_out<T>(h, xf);
   ZArgs<T> z; fill_z(h, z);
+  if (op_level) z.umax_bits = h->sc->umax_scratch;         // the reference's convolution() does not touch calcDt's maxima
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = xf.j_start = z.j_start = js; xi.pb = xf.pb = z.pb = pb;
@@ -328,7 +331,7 @@ static int export_t(chan_handle* h, const void* f, void* phys) {
   return CHAN_OK;
 }
 
-int launch_nonlinear_planes(chan_handle* h) { return h->prec == 4 ? nonlinear_t<float>(h) : nonlinear_t<double>(h); }
+int launch_nonlinear_planes(chan_handle* h, bool op_level) { return h->prec == 4 ? nonlinear_t<float>(h, op_level) : nonlinear_t<double>(h, op_level); }
 int launch_symmetrize(chan_handle* h, void* a, void* b) { return h->prec == 4 ? symmetrize_t<float>(h, a, b) : symmetrize_t<double>(h, a, b); }
 int launch_to_physical(chan_handle* h, const void* f, void* phys) { return h->prec == 4 ? export_t<float>(h, f, phys) : export_t<double>(h, f, phys); }
 

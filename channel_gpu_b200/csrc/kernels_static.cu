@@ -25,8 +25,16 @@
 //    kernels overlap on the GPU (different streams, different handles, different
 //    host threads) race on it.  Serialise them.
 //
-// The arithmetic is that of chan_deriv_y (same y tables, same sweep order), so
-// results agree bit for bit on the same pencils.
+//  * u_dev must be complete before the call: the kernel runs on the handle's own
+//    non-blocking stream, which is not ordered after the caller's streams.  The
+//    call returns after the kernel has finished (it synchronises that stream).
+//  * one thread walks one pencil, so its loads are 2*NY elements apart between
+//    neighbouring threads (uncoalesced): fine for the small batches this entry
+//    point is limited to, not a substitute for the fused path.
+//
+// The arithmetic is that of chan_deriv_y (same y tables, same sweep order and
+// operations per row): fp64 results are identical to it on the same pencils
+// (tests/test_zz_no_alloc.py asserts equality).
 #include "chan_internal.h"
 
 namespace chan {
@@ -41,9 +49,11 @@ static __device__ __align__(256) double g_static_scratch[CHAN_STATIC_SCRATCH_DOU
 static const int kMaxDevices = 64;
 static double* g_scratch_addr[kMaxDevices];
 
+// The address is looked up for the HANDLE's device (the one its stream and tables live on), whatever
+// device the calling thread has current: that device is made current for the lookup and for the
+// launch that follows, and the caller's device is restored before returning.
 static int static_scratch_for_device(chan_handle* h, double** out) {
-  int dev = -1;
-  CHAN_CUDA(h, cudaGetDevice(&dev));
+  const int dev = h->device;
   if (dev < 0 || dev >= kMaxDevices) return set_err(h, CHAN_ERR_ARG, "device ordinal %d outside the supported range", dev);
   if (!g_scratch_addr[dev]) {
     double* p = 0;
@@ -100,14 +110,20 @@ extern "C" int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_p
                    "(at most %ld pencils per call at this NY)",
                    n_pencils, ny, (double)n_chain * ny, (unsigned)CHAN_STATIC_SCRATCH_DOUBLES,
                    (long)(CHAN_STATIC_SCRATCH_DOUBLES / (2u * (unsigned)ny)));
+  int caller_dev = -1;
+  CHAN_CUDA(h, cudaGetDevice(&caller_dev));
+  if (caller_dev != h->device) CHAN_CUDA(h, cudaSetDevice(h->device));
   double* scratch = 0;
   int rc = static_scratch_for_device(h, &scratch);
-  if (rc) return rc;
-  unsigned grid = (unsigned)((n_chain + 127) / 128);
-  if (h->prec == 4) deriv_y_pencils_kernel<float><<<grid, 128, 0, h->stream>>>((float*)u_dev, scratch, h->yt.d1[0], ny, n_chain);
-  else deriv_y_pencils_kernel<double><<<grid, 128, 0, h->stream>>>((double*)u_dev, scratch, h->yt.d1[0], ny, n_chain);
-  h->launches++;
-  CHAN_CUDA(h, cudaGetLastError());
-  CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
-  return CHAN_OK;
+  if (!rc) {
+    unsigned grid = (unsigned)((n_chain + 127) / 128);
+    if (h->prec == 4) deriv_y_pencils_kernel<float><<<grid, 128, 0, h->stream>>>((float*)u_dev, scratch, h->yt.d1[0], ny, n_chain);
+    else deriv_y_pencils_kernel<double><<<grid, 128, 0, h->stream>>>((double*)u_dev, scratch, h->yt.d1[0], ny, n_chain);
+    h->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) rc = set_err(h, CHAN_ERR_CUDA, "chan_deriv_y_pencils_static: %s", cudaGetErrorString(e));
+  }
+  if (caller_dev != h->device) cudaSetDevice(caller_dev);
+  return rc;
 }

@@ -106,8 +106,7 @@ static int upload_perms(chan_handle* h, FftPlan& p, int** dinv, int** dpos) {
 // Radix schedule: fewest stages (>= 2) out of {16,12,8,6,4,3,2}, then the largest smallest radix.
 // small_last: the last stage is fused with the pointwise product in z and must be 4, 3 or 2
 // (6 lines x r_L complex values live in registers).
-static int g_max_radix = 16;
-static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int* bestmin, bool small_last) {
+static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int* bestmin, bool small_last, int max_radix) {
   static const int cand[7] = { 16, 12, 8, 6, 4, 3, 2 };
   if (n == 1) {
     if (depth != maxdepth) return false;
@@ -121,17 +120,16 @@ static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int
   bool found = false;
   for (int c = 0; c < 7; c++) {
     int r = cand[c];
-    if (n % r || r > g_max_radix) continue;
+    if (n % r || r > max_radix) continue;
     if (depth > 0 && r > cur[depth - 1]) continue;      // non-increasing: each multiset once
     cur[depth] = r;
-    if (plan_search(n / r, depth + 1, maxdepth, cur, best, bestmin, small_last)) found = true;
+    if (plan_search(n / r, depth + 1, maxdepth, cur, best, bestmin, small_last, max_radix)) found = true;
   }
   return found;
 }
 void make_plan(FftPlan* p, int n, bool small_last, int max_radix) {
-  g_max_radix = max_radix;
   int cur[16], best[16], bestmin = 0, ns = 0;
-  for (int d = 2; d <= 12 && !ns; d++) { bestmin = 0; if (plan_search(n, 0, d, cur, best, &bestmin, small_last)) ns = d; }
+  for (int d = 2; d <= 12 && !ns; d++) { bestmin = 0; if (plan_search(n, 0, d, cur, best, &bestmin, small_last, max_radix)) ns = d; }
   p->n = ns ? n : -1; p->nstage = ns;
   if (!ns) return;
   if (small_last) {     // move the largest radix <= 4 to the end

@@ -9,7 +9,7 @@ LIBDIR = os.path.join(HERE, "..", "channel_gpu_b200", "lib")
 
 
 def build_host():
-    srcs = [os.path.join(HERE, f) for f in ("conf.c", "driver.c")]
+    srcs = [os.path.join(HERE, f) for f in ("conf.c", "driver.c", "h5min.c", "checkpoint.c")]
     common = ["-O2", "-std=c99", "-Wall", "-D_POSIX_C_SOURCE=200809L", "-fPIC"]
     link = ["-L" + LIBDIR, "-lchannel_b200", "-Wl,-rpath," + os.path.abspath(LIBDIR), "-lm"]
     so = os.path.join(HERE, "libchannel_host.so")

@@ -142,4 +142,9 @@ void read_run_opts_from_config(run_opts_t* o, const config_t* c) {
   int iv;
   if (conf_lookup_int(c, "application.REYNOLDS", &iv)) o->reynolds = iv;
   if (conf_lookup_int(c, "application.FIXED_DT", &iv)) o->fixed_dt = iv;
+  o->checkpoint_every = 0; strcpy(o->checkpoint, "-"); strcpy(o->restart, "-");
+  conf_lookup_int(c, "application.checkpoint.EVERY", &o->checkpoint_every);
+  const char* sv;
+  if (conf_lookup_string(c, "application.checkpoint.FILE", &sv)) { strncpy(o->checkpoint, sv, sizeof(o->checkpoint) - 1); o->checkpoint[sizeof(o->checkpoint) - 1] = 0; }
+  if (conf_lookup_string(c, "application.checkpoint.RESTART", &sv)) { strncpy(o->restart, sv, sizeof(o->restart) - 1); o->restart[sizeof(o->restart) - 1] = 0; }
 }

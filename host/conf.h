@@ -23,6 +23,9 @@ typedef struct run_opts_t {
   double fixed_dt;   /* application.FIXED_DT   0 = calcDt          */
   int nsteps;        /* application.NSTEPS     RK3.c:124     30000 */
   int precision;     /* application.PRECISION  4 | 8         4     */
+  int checkpoint_every;    /* application.checkpoint.EVERY    steps between checkpoints, 0 = none (the reference has none) */
+  char checkpoint[100];    /* application.checkpoint.FILE     written every EVERY steps (one rank's full state)      */
+  char restart[100];       /* application.checkpoint.RESTART  "-" or absent = start from the input fields           */
 } run_opts_t;
 
 int  conf_parse_text(config_t* c, const char* text);          /* 0 = ok; else c->error / c->error_line */

@@ -1,4 +1,6 @@
 #include "driver.h"
+#include "h5min.h"
+#include <stdint.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -25,6 +27,21 @@ int write_field_raw(const char* name, const void* src, size_t bytes) {
   size_t put = fwrite(src, 1, bytes, f); fclose(f);
   if (put != bytes) { fprintf(stderr, "\nwriting error: %s", name); return -1; }
   return 0;
+}
+static int is_h5(const char* name) { size_t n = strlen(name); return n > 3 && !strcmp(name + n - 3, ".h5"); }
+int read_field(const char* name, void* dst, int nx, int ny, int nz, int precision) {
+  if (!is_h5(name)) return read_field_raw(name, dst, (size_t)nx * ny * nz * 2 * precision);
+  const uint64_t dims[3] = { (uint64_t)nx, (uint64_t)ny, (uint64_t)(2 * nz) };      /* hit_mpi.c:272-279, io.c:48-54 */
+  int rc = h5min_read(name, dst, precision, dims);
+  if (rc) fprintf(stderr, "\nerror lectura: %s (%s)", name, rc == -2 ? "dataset u has another type or shape" : "not a readable HDF5 file");
+  return rc;
+}
+int write_field(const char* name, const void* src, int nx, int ny, int nz, int precision) {
+  if (!is_h5(name)) return write_field_raw(name, src, (size_t)nx * ny * nz * 2 * precision);
+  const uint64_t dims[3] = { (uint64_t)nx, (uint64_t)ny, (uint64_t)(2 * nz) };
+  int rc = h5min_write(name, src, precision, dims);
+  if (rc) fprintf(stderr, "\nerror escritura: %s", name);
+  return rc;
 }
 int read_umean(const char* name, void* dst, int ny, int precision) { return read_field_raw(name, dst, (size_t)ny * 2 * precision); }
 int write_umean(const char* name, const void* src, int ny, int precision) { return write_field_raw(name, src, (size_t)ny * 2 * precision); }
@@ -111,7 +128,7 @@ int run_channel(const domain_t* d, const paths_t* p, const run_opts_t* o, int ve
     gen_rand_data(ddv, g, (double)d->nx, n, o->precision);
   } else {
     if (verbose) printf("Reading Data...\nReading: %s, %s\n", p->ginput, p->ddvinput);
-    if (read_field_raw(p->ginput, g, bytes) || read_field_raw(p->ddvinput, ddv, bytes)) { chan_destroy(h); return 1; }
+    if (read_field(p->ginput, g, d->nx, d->ny, d->nz, o->precision) || read_field(p->ddvinput, ddv, d->nx, d->ny, d->nz, o->precision)) { chan_destroy(h); return 1; }
   }
   CK(chan_set_fields(h, ddv, g));
   if (strcmp(p->umeaninput, "-")) {                                     /* main.c:119-123 */
@@ -122,7 +139,14 @@ int run_channel(const domain_t* d, const paths_t* p, const run_opts_t* o, int ve
   if (verbose) printf("Starting RK iterations...\n");
   CK(chan_rk_init(h));                                                  /* RK3.c:120-123 */
   double time_elapsed = 0.0;
-  for (int counter = 0; counter < o->nsteps; counter++) {               /* RK3.c:127 */
+  int first = 0;
+  if (o->restart[0] && strcmp(o->restart, "-")) {                       /* continue a checkpointed run bit for bit */
+    if (read_checkpoint_file(h, o->restart)) { fprintf(stderr, "cannot restart from %s: %s\n", o->restart, chan_last_error(h)); chan_destroy(h); return 1; }
+    chan_scalars sc0; CK(chan_get_scalars(h, &sc0));
+    first = sc0.counter; time_elapsed = sc0.time;
+    if (verbose) printf("Restarted from %s at (time,counter)=(%f,%d)\n", o->restart, time_elapsed, first);
+  }
+  for (int counter = first; counter < o->nsteps; counter++) {           /* RK3.c:127 */
     if (counter % 10 == 0) {                                            /* FREC_STATS, nonLinear.c:12-15 */
       CK(chan_statistics(h, st));
       if (append_calcst_files(p->path, st, d->ny, o->precision)) fprintf(stderr, "cannot append statistics under %s\n", p->path);
@@ -138,11 +162,13 @@ int run_channel(const domain_t* d, const paths_t* p, const run_opts_t* o, int ve
       fprintf(stderr, "cannot append mean-flow files under %s\n", p->path);
     time_elapsed += sc.dt;                                              /* dt of the step just taken (RK3.c:179-180) */
     if (verbose) printf("\n(time,counter)=(%f,%d)", time_elapsed, counter + 1);
+    if (o->checkpoint_every > 0 && o->checkpoint[0] && strcmp(o->checkpoint, "-") && (counter + 1) % o->checkpoint_every == 0)
+      if (write_checkpoint_file(h, o->checkpoint)) fprintf(stderr, "cannot write checkpoint %s\n", o->checkpoint);
   }
   CK(chan_get_fields(h, ddv, g));                                       /* writeData (main.c:139) */
   int rc = 0;
-  if (p->goutput[0] && strcmp(p->goutput, "-")) rc |= write_field_raw(p->goutput, g, bytes);
-  if (p->ddvoutput[0] && strcmp(p->ddvoutput, "-")) rc |= write_field_raw(p->ddvoutput, ddv, bytes);
+  if (p->goutput[0] && strcmp(p->goutput, "-")) rc |= write_field(p->goutput, g, d->nx, d->ny, d->nz, o->precision);
+  if (p->ddvoutput[0] && strcmp(p->ddvoutput, "-")) rc |= write_field(p->ddvoutput, ddv, d->nx, d->ny, d->nz, o->precision);
   CK(chan_get_umean(h, um));
   if (p->umeanoutput[0] && strcmp(p->umeanoutput, "-")) rc |= write_umean(p->umeanoutput, um, d->ny, o->precision);   /* writeU (main.c:142) */
   chan_destroy(h); free(ddv); free(g); free(um); free(nm); free(st);

@@ -12,6 +12,13 @@ void gen_rand_data(void* ddv, void* g, double F, size_t n_complex, int precision
  * dataset "u" (hit_mpi.c:272-328); here as a raw file (HDF5 is absent on the box) */
 int read_field_raw(const char* name, void* dst, size_t bytes);
 int write_field_raw(const char* name, const void* src, size_t bytes);
+/* the same payload in the reference's container: HDF5 dataset "u", {NX, NY, 2NZ} of float / double (h5min.h).
+ * read_field / write_field pick the container by the file name: "*.h5" = HDF5, anything else = raw */
+int read_field(const char* name, void* dst, int nx, int ny, int nz, int precision);
+int write_field(const char* name, const void* src, int nx, int ny, int nz, int precision);
+/* checkpoint.c: one rank's complete state (chan_checkpoint_save / _load) to / from a file */
+int write_checkpoint_file(chan_handle* h, const char* name);
+int read_checkpoint_file(chan_handle* h, const char* name);
 /* readU / writeU (meanUevol.c:153-176): NY complex values, raw */
 int read_umean(const char* name, void* dst, int ny, int precision);
 int write_umean(const char* name, const void* src, int ny, int precision);

@@ -63,6 +63,7 @@ typedef struct chan_scalars {
   double umax[3];                     /* max |u|,|v|,|w| (un-normalised) fft.c:143 */
   double utau[2];                     /* meanUevol.c:178-199                      */
   int counter;                        /* steps taken (RK3.c:180)                  */
+  double time;                        /* sum of the dt of the steps taken (RK3.c:126 ignores its `time`) */
 } chan_scalars;
 
 /* field selectors for chan_get_field / chan_set_field (globals of RK3.c:4-12) */
@@ -70,7 +71,14 @@ enum { CHAN_F_DDV = 0, CHAN_F_G, CHAN_F_V, CHAN_F_DV, CHAN_F_R_DDV, CHAN_F_R_G,
        CHAN_F_U, CHAN_F_W, CHAN_F_WX, CHAN_F_WY, CHAN_F_WZ, CHAN_F_COUNT };
 
 int  chan_config_default(chan_config* cfg);
-/* setUp (setUp.c:3-29) + setRK3 (RK3.c:17-50) + setRKmean (meanUevol.c:43-84) */
+/* setUp (setUp.c:3-29) + setRK3 (RK3.c:17-50) + setRKmean (meanUevol.c:43-84).
+ * Sizes: NX and 2NZ-2 must factor into 2s and 3s (the hand-written FFTs have radices 2, 3, 4 and their
+ * composites; the reference, through cuFFT, takes any size), NX even, NX >= 8, NY >= 8, NZ >= 5; NX*8 and
+ * (2NZ-2)*7 complex elements of the state type must fit the 200 KB / 220 KB shared-memory tiles of the x / z
+ * transforms (NX <= 12800, 2NZ-2 <= 2011 in fp64).
+ * Ownership on failure: whenever *out comes back non-NULL the caller owns it, also when the return code is
+ * not CHAN_OK - read chan_last_error(*out), then chan_destroy(*out).  *out is NULL only when the handle
+ * itself could not be allocated (CHAN_ERR_ALLOC) or an argument was NULL. */
 int  chan_create(const chan_config* cfg, chan_handle** out);
 void chan_destroy(chan_handle* h);
 const char* chan_last_error(const chan_handle* h);
@@ -93,8 +101,23 @@ int  chan_get_stage_ms(chan_handle* h, double* ms_out8, long* count_out8);
 int chan_set_fields(chan_handle* h, const void* ddv_host, const void* g_host);
 /* cudaMemcpy D2H + writeData (io.c:37-72) */
 int chan_get_fields(chan_handle* h, void* ddv_host, void* g_host);
+/* One field.  With several ranks (chan_config.size > 1) the array is still the FULL [NX][NZ][NY] array of the run,
+ * as in the reference where every rank holds rows i of its slab (main.c:47): a rank reads / writes only the rows
+ * of its own active-kx slab (rank 0 also zeroes the rows of the truncated kx on output); other rows are not touched. */
 int chan_get_field(chan_handle* h, int which, void* host);
 int chan_set_field(chan_handle* h, int which, const void* host);
+/* The same for a host array that holds just this rank's slab: [Kxl][NZ][NY], rows in active-kx order
+ * ikx0 .. ikx0+Kxl-1 with (ikx0, Kxl) = chan_partition(chan_active_kx(NX), size, rank) and kx = ikx <= NX/3 ? ikx :
+ * ikx - chan_active_kx(NX).  What a memory-sized multi-GPU run uses: no rank ever holds the dense array
+ * (hit_mpi.c:282-328 fans the file out slab by slab for the same reason). */
+int chan_get_field_slab(chan_handle* h, int which, void* host_slab);
+int chan_set_field_slab(chan_handle* h, int which, const void* host_slab);
+/* DEVICE pointers to full reference-layout arrays (the ddv, g of main.c:102-103): the coarse RKstep seam without a
+ * bounce through the host.  chan_get_field(s)_dev clears the whole array first and is single-GPU only. */
+int chan_set_fields_dev(chan_handle* h, const void* ddv_dev, const void* g_dev);
+int chan_get_fields_dev(chan_handle* h, void* ddv_dev, void* g_dev);
+int chan_set_field_dev(chan_handle* h, int which, const void* dev);
+int chan_get_field_dev(chan_handle* h, int which, void* dev);
 /* readU / writeU payload (meanUevol.c:153-176): NY complex, .x = <u>(y)*N2 */
 int chan_set_umean(chan_handle* h, const void* umean_host);
 int chan_get_umean(chan_handle* h, void* umean_host);
@@ -105,6 +128,17 @@ int chan_get_scalars(chan_handle* h, chan_scalars* out);
 int chan_set_fixed_dt(chan_handle* h, double dt);
 /* dt of the step about to run (the reference starts with 0, RK3.c:114) */
 int chan_set_dt(chan_handle* h, double dt);
+
+/* ---- checkpoint / restart -------------------------------------------------------
+ * No counterpart in the reference: it restarts from the field files written once at the end of a run (main.c:139,
+ * io.c:37-72) and loses R_phi, R_g, dt and the step count (RK3.c:114), so a restarted run is not the continued
+ * run.  Here one rank's complete state (phi, g, v, dv, R_phi, R_g, mean profile, N_old, every step scalar, the
+ * symmetry cadence counter) goes into one host buffer of chan_checkpoint_bytes() bytes; loading it into a handle
+ * created with the same grid / precision / rank / size continues bit for bit (tests/test_gpu_checkpoint.py).
+ * The payload is versioned and private to the library (compact layout); host/checkpoint.c writes it to a file. */
+size_t chan_checkpoint_bytes(const chan_handle* h);
+int chan_checkpoint_save(chan_handle* h, void* host_buf);
+int chan_checkpoint_load(chan_handle* h, const void* host_buf);
 
 /* ---- the hot path ---------------------------------------------------------- */
 /* RKstep prologue (RK3.c:120-123): dealias, imposeSymetry, calcVdV */
@@ -149,7 +183,12 @@ int chan_fft_backward_transpose(chan_handle* h, const void* u_dev, void* phys_de
  * 2097152 doubles, otherwise CHAN_ERR_ARG is returned and nothing runs.  The call makes
  * no cudaMalloc/cudaFree and no allocating library call.  The first call on a device
  * resolves the array's address: issue it before any stream capture.  All calls share
- * the array, so calls that may overlap on the GPU must be serialised by the caller. */
+ * the array, so calls that may overlap on the GPU must be serialised by the caller.
+ * The kernel runs on the handle's device and private stream whatever device the
+ * calling thread has current (it is switched and restored); u_dev must be complete
+ * before the call (that stream is not ordered after the caller's), and the call
+ * returns once the kernel has finished.  One thread walks one pencil, so the loads
+ * are uncoalesced: meant for small batches, not as a substitute for the fused path. */
 int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_pencils);
 
 /* ---- multi-GPU peer-store exchange (no counterpart in the reference, which stages every transpose
