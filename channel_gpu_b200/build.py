@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libchannel_b200.so")
-SOURCES = ["api.cu", "kernels_tables.cu", "kernels_pencil.cu", "kernels_pencil_seg.cu", "kernels_plane.cu", "kernels_misc.cu", "kernels_static.cu", "comm.cu"]
+SOURCES = ["api.cu", "kernels_tables.cu", "kernels_pencil.cu", "kernels_pencil_seg.cu", "kernels_pencil_lanes.cu", "kernels_plane.cu", "kernels_misc.cu", "kernels_static.cu", "comm.cu"]
 NVCC = os.environ.get("NVCC", "nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC"]

@@ -86,6 +86,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1, false },
       { "CHAN_TUNE_PRE_SCATTER", &h->tune.pre_scatter, 0, false },
       { "CHAN_TUNE_LANES", &h->tune.lanes, -1, false },
+      { "CHAN_TUNE_LANES_S", &h->tune.lanes_s, 4, false },
+      { "CHAN_TUNE_LANES_MB", &h->tune.lanes_mb, 0, false },
       // timing ablation: kernels return early (results are garbage) - only in -DCHAN_ABLATE builds
       { "CHAN_TUNE_Z_STOP", &h->tune.z_stop, 0, true },
       { "CHAN_TUNE_X_SKIP", &h->tune.x_skip, 0, true },
@@ -175,6 +177,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || cfg->size > 1) ? 1 : 0;
   if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
+  // on-chip y stage (one warp per mode, lanes along y): bit 0 = post.  CHAN_TUNE_LANES: -1 = wherever it is supported
+  if (h->tune.lanes < 0) h->tune.lanes = 1;
+  if (h->tune.lanes && lanes_supported(h)) { if ((rc = lanes_setup(h))) return rc; } else h->tune.lanes = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
 }
@@ -187,7 +192,7 @@ extern "C" void chan_destroy(chan_handle* h) {
     for (int f = 0; f < 3; f++) if (h->peer_H[r][f]) cudaIpcCloseMemHandle(h->peer_H[r][f]);
   }
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
-                   h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
+                   h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->ln.tabs, h->ln.pivH, h->ln.pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->stat_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
@@ -489,7 +494,8 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   }
   CHAN_CUDA(h, cudaEventRecord(h->ev_join, h->aux));
   t = t_begin(h, CHAN_STAGE_POST);
-  rc = (h->tune.pencil_seg & 2) ? launch_pencil_post_seg(h, n) : launch_pencil_post(h, n);   // RK explicit + h_v,h_g + implicit + bi-Laplacian
+  rc = (h->tune.lanes & 1) ? launch_pencil_post_lanes(h, n)
+     : ((h->tune.pencil_seg & 2) ? launch_pencil_post_seg(h, n) : launch_pencil_post(h, n));   // RK explicit + h_v,h_g + implicit + bi-Laplacian
   t_end(h, t);
   CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
   return rc;

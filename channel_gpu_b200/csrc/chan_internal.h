@@ -111,6 +111,9 @@ struct chan_handle {
   // segment-parallel y stage (kernels_pencil_seg.cu): segment length, prefix-product tables of the
   // folded d/dy LU for that length, per-mode pivots of the Helmholtz / implicit matrices [NY][M]
   int seg_S; double *seg_pf, *seg_pb; double *pivH, *pivI; int pivH_ready;
+  // on-chip y stage (kernels_pencil_lanes.cu): rows per lane, warps per mode, padded rows, staging column pitch, modes per
+  // block, padded y tables, pivot tables [M][NYL] of the Helmholtz / implicit matrices
+  struct { int S, W, NYL, NYP, MB; double* tabs; double *pivH, *pivI; int pivH_ready; } ln;
   void *tw_x, *tw_z; chan::FftPlan px, pz;
   int *invx, *invz, *posx, *posz;   // digit-reversal tables of the two plans
   void *mean_a, *mean_b;        // host-mesh differences in T (meanUevol.c:230-231)
@@ -126,7 +129,7 @@ struct chan_handle {
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;   // the rank's slab [Kxl][NZ][NY] of the reference layout
   double* stat_buf;             // 4*NY sums of chan_statistics
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_scatter, lanes; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_scatter, lanes, lanes_s, lanes_mb; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
@@ -164,6 +167,10 @@ int seg_supported(chan_handle* h);
 int seg_setup(chan_handle* h);
 int launch_pencil_pre_seg(chan_handle* h);
 int launch_pencil_post_seg(chan_handle* h, int n);
+// kernels_pencil_lanes.cu
+int lanes_supported(chan_handle* h);
+int lanes_setup(chan_handle* h);
+int launch_pencil_post_lanes(chan_handle* h, int n);
 // kernels_plane.cu
 int launch_nonlinear_planes(chan_handle* h, bool op_level = false);   // u,v,w,omega -> H (in ox,oy,oz); op_level: inputs sit in the local pencil fields, step scalars untouched
 int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields

@@ -104,16 +104,18 @@ def test_rk3_steps_vs_reference_build(cg, case, sub, n, fixed, tol):
 # (bit-identical), and so does any FFT launch shape; the segment-parallel register kernels compose affine maps
 # instead of sweeping sequentially (round-off level differences).  The knobs are read by chan_create from the
 # environment (channel_gpu_b200/csrc/api.cu).
-CHAIN = {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0"}
+CHAIN = {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0"}
 SAME_BITS_AS_CHAIN = [
-    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "1"},      # deep-batch post
-    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "2"},      # three-role post
-    {"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0", "CHAN_TUNE_Z_THREADS": "256", "CHAN_TUNE_Z_XP": "2",
+    {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "1"},      # deep-batch post
+    {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "2"},      # three-role post
+    {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0", "CHAN_TUNE_Z_THREADS": "256", "CHAN_TUNE_Z_XP": "2",
      "CHAN_TUNE_X_THREADS": "256", "CHAN_TUNE_X_TK": "4"},          # other FFT launch shapes
 ]
 ROUND_OFF_OF_CHAIN = [
-    {"CHAN_TUNE_PENCIL_SEG": "1", "CHAN_TUNE_POST_DEEP": "0"},      # register pre
-    {"CHAN_TUNE_PENCIL_SEG": "3"},                                  # register pre and post
+    {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "1", "CHAN_TUNE_POST_DEEP": "0"},      # register pre
+    {"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "3"},                                  # register pre and post
+    {"CHAN_TUNE_LANES": "1", "CHAN_TUNE_PENCIL_SEG": "0"},                                  # on-chip post (one warp per mode, lanes along y)
+    {"CHAN_TUNE_LANES": "3"},                                                               # on-chip pre and post
     {},                                                             # whatever the size heuristics pick
 ]
 
@@ -195,18 +197,21 @@ def test_wall_normal_sweep_vs_oracle_and_variants(cg, monkeypatch, ny):
             monkeypatch.delenv(k)
         return out
 
-    chain = run({"CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0"})
+    chain = run({"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "0", "CHAN_TUNE_POST_DEEP": "0"})
     tol = {"ddv": 5e-6, "g": 1e-8, "v": 1e-7, "dv": 1e-6, "R_ddv": 5e-6, "R_g": 1e-7}
     for name, t in tol.items():
         assert rel(chain[name], getattr(S, name)) < t, name
     auto = run({})
-    regs = run({"CHAN_TUNE_PENCIL_SEG": "3"})
+    regs = run({"CHAN_TUNE_LANES": "0", "CHAN_TUNE_PENCIL_SEG": "3"})
+    print("\nNY=%d on-chip y stage vs thread-per-chain: " % ny + " ".join("%s=%.1e" % (k, rel(auto[k], chain[k])) for k in names))
     for name in names:
-        assert rel(auto[name], chain[name]) < 1e-12, name
-        # The register `post` (off by default) forms R_phi = hv' - kk H2 from a derivative obtained by composing
-        # affine maps: its round-off grows with NY (1e-13 at 97, 1e-11 at 385, 5e-11 at 633; scripts/seg_vs_chain.py),
-        # which is one more reason the library never picks it on its own.
-        assert rel(regs[name], chain[name]) < (1e-10 if name == "R_ddv" else 1e-12), name
+        # R_phi = d/dy[-i(k1 H1 + k3 H3)] - kk H2 differentiates the nonlinear term, round-off included: H differs between
+        # two implementations at 1e-13..1e-12 after a substep (v, dv do) and d/dy on the stretched grid amplifies that
+        # noise by ~NY/h_min, so R_phi of two CORRECT kernels differs by 2e-13 (NY=97) .. 7e-11 (NY=633).  Against the
+        # same expression in extended precision both are at 1e-14..5e-14 (scripts/lanes_precision.py,
+        # profiles/r02_lanes_notes.txt): the bound below is the noise amplification, not a kernel error.
+        assert rel(auto[name], chain[name]) < (2e-10 if name == "R_ddv" else 1e-12), name
+        assert rel(regs[name], chain[name]) < (2e-10 if name == "R_ddv" else 1e-12), name
 
 
 @pytest.mark.parametrize("grid", [(48, 17, 385), (64, 17, 193), (32, 17, 65), (96, 17, 97), (48, 17, 49)])
