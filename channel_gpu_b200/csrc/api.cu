@@ -126,7 +126,11 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (cfg->device >= 0) CHAN_CUDA(h, cudaSetDevice(cfg->device));
   CHAN_CUDA(h, cudaGetDevice(&h->device));
   CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking));
+  {   // the side stream carries one-block kernels that must not queue behind a GPU-filling kernel of the main stream
+    int lo = 0, hi = 0;
+    CHAN_CUDA(h, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, hi));
+  }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   int rc;
@@ -177,8 +181,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || cfg->size > 1) ? 1 : 0;
   if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
-  // on-chip y stage (one warp per mode, lanes along y): bit 0 = post.  CHAN_TUNE_LANES: -1 = wherever it is supported
-  if (h->tune.lanes < 0) h->tune.lanes = 1;
+  // on-chip y stage (warps per mode, lanes along y; kernels_pencil_lanes.cu): bit 0 = post, bit 1 = pre.  It needs a
+  // third of the DRAM traffic and has 32..160 threads per mode, but executes more instructions per mode than the
+  // thread-per-chain kernels: measured on B200 it wins where a rank holds few chains (many GPUs / small grids: Re_tau=550
+  // on 8 GPUs: pre 0.080 -> 0.053 ms, post 0.379 -> 0.218 ms per substep) and loses on a GPU full of chains
+  // (Re_tau=550 on one GPU: post 0.80 -> 1.04 ms), profiles/r02_lanes_notes.txt.  CHAN_TUNE_LANES overrides.
+  if (h->tune.lanes < 0) h->tune.lanes = (2 * d.M < 148L * 128) ? 3 : 0;
   if (h->tune.lanes && lanes_supported(h)) { if ((rc = lanes_setup(h))) return rc; } else h->tune.lanes = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
@@ -474,7 +482,8 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if (!h || n < 0 || n > 2) return CHAN_ERR_ARG;
   int rc, t;
   t = t_begin(h, CHAN_STAGE_PRE);
-  if ((rc = (h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
+  if ((rc = (h->tune.lanes & 2) ? launch_pencil_pre_lanes(h)
+          : ((h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h)))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
   t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
   t_end(h, t);

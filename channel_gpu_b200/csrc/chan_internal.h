@@ -171,6 +171,7 @@ int launch_pencil_post_seg(chan_handle* h, int n);
 int lanes_supported(chan_handle* h);
 int lanes_setup(chan_handle* h);
 int launch_pencil_post_lanes(chan_handle* h, int n);
+int launch_pencil_pre_lanes(chan_handle* h);
 // kernels_plane.cu
 int launch_nonlinear_planes(chan_handle* h, bool op_level = false);   // u,v,w,omega -> H (in ox,oy,oz); op_level: inputs sit in the local pencil fields, step scalars untouched
 int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields

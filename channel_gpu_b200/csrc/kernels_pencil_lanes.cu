@@ -500,6 +500,113 @@ __global__ void __launch_bounds__(512, 1) pencil_post_lanes_kernel(PArgs<T> a, L
   }
 }
 
+// =====================================================================================================================
+// pencil_pre: (dv, g, v, <u>) -> u, w, omega_x, omega_y, omega_z: calcUW (nonLinear_kernels.cu:8-92) + writeUmean
+// (meanUevol.c:117-125) + the two deriv_Y of convolution.c:7-11 + readUtau (:14-16) + calcOmega
+// (convolution_kernels.cu:7-66).  With several GPUs the six plane-stage inputs of row j leave the staging tiles as whole
+// row segments straight into the receive buffers of the rank that owns plane j (NVLink stores: the pencil -> plane
+// transpose of channel_cuda_mpi.c:95-128); every row of the block is in flight at once, so the stores spread over all
+// destinations.
+// =====================================================================================================================
+template <typename T, int S>
+__global__ void __launch_bounds__(512, 1) pencil_pre_lanes_kernel(PArgs<T> a, LaneTabs t, PeerOut po) {
+  typedef typename Vec2<T>::type T2;
+  const int W = t.W, MB = t.MB, NYP = t.NYP, ny = a.ny;
+  const int ncol = 2 * MB, lgcol = 31 - __clz(ncol);
+  T* const tl = (T*)lanes_smem;                                  // 6 tiles: dv -> u, g -> w, v, omega_x, omega_y, omega_z
+  const size_t tsz = (size_t)ncol * NYP;
+  T* const tU = tl; T* const tW = tl + tsz; T* const tV = tl + 2 * tsz; T* const tOx = tl + 3 * tsz; T* const tOy = tl + 4 * tsz; T* const tOz = tl + 5 * tsz;
+  double* const xch_all = (double*)(tl + 7 * tsz + (((7 * tsz) & 1) ? 1 : 0));   // same carve-up as pencil_post
+  const long st = 2 * a.M, e0 = (long)blockIdx.x * ncol, elim = 2 * a.M;
+  {
+    T* const tA[3] = { tU, tW, tV };
+    const T* const sA[3] = { (const T*)a.dv, (const T*)a.g, (const T*)a.v };
+    stage_in<T, S, 3>(tA, sA, st, e0, elim, lgcol, ny, NYP);
+    cp_async_commit();
+  }
+  LCtx c;
+  const int warp = threadIdx.x >> 5;
+  c.lane = threadIdx.x & 31; c.W = W; c.mi = warp / W; c.ww = warp - c.mi * W; c.L = c.ww * 32 + c.lane; c.j0 = c.L * S; c.ny = ny; c.NL = t.NL;
+  c.xch = xch_all + (size_t)c.mi * 2 * W * XW; c.par = 0;
+  long m = (long)blockIdx.x * MB + c.mi;
+  const bool live = m < a.M;
+  if (!live) m = a.M - 1;
+  const int ikx = a.ikx0 + (int)(m / a.Kz), kzi = (int)(m % a.Kz);
+  const int kxi = ikx <= a.kxmax ? ikx : ikx - a.Kx;
+  const bool zero_mode = (kxi == 0 && kzi == 0);
+  const T k1 = a.k1fac * (T)kxi, k3 = a.k3fac * (T)kzi, kk = k1 * k1 + k3 * k3;
+  const T rkk = zero_mode ? (T)1 : (T)1 / kk;
+  const bool with_mean = zero_mode && a.use_mean;
+  const int col0 = (2 * c.mi) * NYP + cseg<S>(c.L), col1 = col0 + NYP;
+  bool rowok[S];
+#pragma unroll
+  for (int r = 0; r < S; r++) rowok[r] = c.j0 + r < ny;
+  cp_async_wait<0>();
+  __syncthreads();
+  // u = i (k1 dv - k3 g)/kk, w = i (k3 dv + k1 g)/kk (uw_comp of pencil_common.cuh, both components of the mode)
+  T u[2][S], w[2][S];
+  double f[4][S];
+#pragma unroll
+  for (int r = 0; r < S; r++) {
+    const T z = (T)0;
+    const T dre = rowok[r] ? tU[col0 + r] : z, dim = rowok[r] ? tU[col1 + r] : z, gre = rowok[r] ? tW[col0 + r] : z, gim = rowok[r] ? tW[col1 + r] : z;
+#pragma unroll
+    for (int cc = 0; cc < 2; cc++) {
+      const T s = cc ? (T)1 : (T)-1, dp = cc ? dre : dim, gp = cc ? gre : gim;      // the other component
+      if (sizeof(T) == 8) { u[cc][r] = s * (k1 * dp - k3 * gp) * rkk; w[cc][r] = s * (k3 * dp + k1 * gp) * rkk; }
+      else { const T kd = zero_mode ? (T)1 : kk; u[cc][r] = s * (k1 * dp - k3 * gp) / kd; w[cc][r] = s * (k3 * dp + k1 * gp) / kd; }
+      if (zero_mode) { u[cc][r] = 0; w[cc][r] = 0; }
+    }
+    if (with_mean) { u[0][r] = rowok[r] ? a.mean_u[c.j0 + r] : z; u[1][r] = 0; }    // writeUmean (nonLinear.c:19-21)
+    f[0][r] = (double)u[0][r]; f[1][r] = (double)u[1][r]; f[2][r] = (double)w[0][r]; f[3][r] = (double)w[1][r];
+  }
+  d1_lanes<S, 4>(c, t, f);
+#pragma unroll
+  for (int r = 0; r < S; r++) {
+    const T z = (T)0;
+    const T vre = rowok[r] ? tV[col0 + r] : z, vim = rowok[r] ? tV[col1 + r] : z;
+#pragma unroll
+    for (int cc = 0; cc < 2; cc++) {
+      const T s = cc ? (T)1 : (T)-1;
+      const T dudy = (T)f[cc][r], dwdy = (T)f[2 + cc][r];
+      const T vp = cc ? vre : vim, up = u[cc ^ 1][r], wp = w[cc ^ 1][r];
+      if (rowok[r]) {
+        const int o = (cc ? col1 : col0) + r;
+        tOx[o] = dwdy - s * k3 * vp;                    // omega_x = dw/dy - i k3 v   (calcOmegakernel, convolution_kernels.cu:46-53)
+        tOy[o] = s * (k3 * up - k1 * wp);               // omega_y = i (k3 u - k1 w)
+        tOz[o] = -dudy + s * k1 * vp;                   // omega_z = -du/dy + i k1 v
+        tU[o] = u[cc][r]; tW[o] = w[cc][r];
+      }
+      if (zero_mode && cc == 0 && a.sc && live) {        // readUtau (convolution.c:14-16)
+        if (c.j0 + r == 0) a.sc->dudy_wall[0] = (double)dudy;
+        if (c.j0 + r == ny - 1) a.sc->dudy_wall[1] = (double)dudy;
+      }
+    }
+  }
+  __syncthreads();
+  // a thread keeps one column and walks down the rows (stage_out), choosing the destination per row
+  const int cc = threadIdx.x & (ncol - 1), dj = blockDim.x >> lgcol;
+  if (e0 + cc >= elim) return;
+  const int cb = cc * NYP;
+  const bool omega_only = a.op == OP_OMEGA;
+  for (int j = threadIdx.x >> lgcol; j < ny; j += dj) {
+    const int so = cb + cpos<S>(j);
+    const T vu = tU[so], vw = tW[so], vv = tV[so], v1 = tOx[so], v2 = tOy[so], v3 = tOz[so];
+    if (po.nranks > 1) {
+      int p = 0;
+#pragma unroll
+      for (int i = 1; i < 8; i++) p += (i < po.nranks && j >= po.part_j[i]) ? 1 : 0;
+      const long idx = 2 * (po.src_off[p] + (long)(j - po.part_j[p]) * a.M) + e0 + cc;
+      ((T*)po.rcv[p][0])[idx] = vu; ((T*)po.rcv[p][1])[idx] = vv; ((T*)po.rcv[p][2])[idx] = vw;
+      ((T*)po.rcv[p][3])[idx] = v1; ((T*)po.rcv[p][4])[idx] = v2; ((T*)po.rcv[p][5])[idx] = v3;
+    } else {
+      const long go = (long)j * st + e0 + cc;
+      if (!omega_only) { ((T*)a.u)[go] = vu; ((T*)a.w)[go] = vw; }
+      ((T*)a.ox)[go] = v1; ((T*)a.oy)[go] = v2; ((T*)a.oz)[go] = v3;
+    }
+  }
+}
+
 // Pivots of (A - kk M) [implicit = 0] or (M - D(A - kk M)) [implicit = 1] for the upward elimination, one thread per
 // mode, rows in order: piv[m*NYL + j] = 1/(d_j - l_j c_(j-1)), 0 on the wall rows (identity rows with zero right-hand
 // side) and on the padding.
@@ -617,6 +724,21 @@ static int post_lanes_t(chan_handle* h, int n) {
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
 }
+
+template <typename T, int S>
+static int pre_lanes_t(chan_handle* h) {
+  PArgs<T> a; fill_pencil_args<T>(h, a);
+  LaneTabs t; fill_lane_tabs(h, t);
+  PeerOut po; fill_peer_out(h, po);
+  const size_t sm = lanes_smem_bytes(h, 7, t.MB, t.NYP);
+  CHAN_CUDA(h, cudaFuncSetAttribute(pencil_pre_lanes_kernel<T, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  const unsigned grid = (unsigned)((h->d.M + t.MB - 1) / t.MB);
+  pencil_pre_lanes_kernel<T, S><<<grid, t.MB * t.W * 32, sm, h->stream>>>(a, t, po);
+  h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+int launch_pencil_pre_lanes(chan_handle* h) { return h->prec == 4 ? pre_lanes_t<float, 4>(h) : pre_lanes_t<double, 4>(h); }
 
 int launch_pencil_post_lanes(chan_handle* h, int n) {
   return h->prec == 4 ? post_lanes_t<float, 4>(h, n) : post_lanes_t<double, 4>(h, n);

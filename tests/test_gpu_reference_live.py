@@ -242,8 +242,11 @@ def test_window_100_steps_statistics_vs_reference_files(short_tmp):
         want = sum(_floats(out + "ref/" + name), []); got = sum(_floats(out + "ours/" + name), [])
         assert len(want) == nval and len(got) == nval, (name, len(want), len(got))
         a, b = np.array(got), np.array(want)
-        assert np.array_equal(np.isnan(a), np.isnan(b)), name            # sqrt of a negative Reynolds stress (Q14)
-        ok = ~np.isnan(b)
+        # RSTRSS.dat prints sqrt(-<uv>), i.e. -nan wherever the stress is negative (Q14): the patterns must agree except
+        # where the stress is zero to round-off (walls, centre line) and its sign is anybody's guess
+        flip = np.isnan(a) != np.isnan(b)
+        assert np.all(np.nan_to_num(np.where(flip, np.where(np.isnan(a), b, a), 0.0)) < 1e-3), name
+        ok = ~np.isnan(b) & ~np.isnan(a)
         scale = np.abs(b[ok]).max()
         report[name] = float(np.abs(a[ok] - b[ok]).max() / scale)
         # the files carry 6 decimals (" %f", "%e"): agreement to print precision relative to the file's own scale
