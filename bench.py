@@ -212,7 +212,7 @@ def run_reference(args, cfg):
             "config": {"workload": cfg["name"] + (", fp64 state" if args.precision == 8 else ", fp32 state") + ", 1 GPU", "grid": [cfg["nx"], cfg["ny"], cfg["nz"]],
                        "ranks": 1, "requested_gpus": args.gpus,
                        "note": "reference CUDA build (cuFFT/cuSPARSE/cuBLAS, host-staged transposes), ONE rank on one GPU whatever --gpus says: its slab "
-                               "code needs NY%size==0 (channel.h:72-73; every BASELINE NY is odd) and no MPI exists on the box, so at N>1 this "
+                               "code needs NY%%size==0 (channel.h:72-73; every BASELINE NY is odd) and no MPI exists on the box, so at N>1 this "
                                "arm is a one-GPU number; steps timed: %d of the %d asked for (bounded sample)" % (steps, args.steps)}}
     if not os.path.exists(b):
         base.update({"unavailable": "reference binary %s not built (oracle/build_ref.sh needs /root/reference)" % os.path.basename(b)})

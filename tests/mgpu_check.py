@@ -54,6 +54,20 @@ def main():
         st = ch.statistics()
         if not np.isfinite(st).all():
             sys.exit(1)
+        # operator-level convolution on a multi-GPU handle (inputs sit in the local pencil fields, whatever exchange the
+        # substep uses) against the reference build's dump; it must leave the step scalars alone
+        if g.has("ops/conv_wx"):
+            before = ch.scalars()
+            H = ch.convolution(g.full("ops/uw_u"), g.full("ops/v0"), g.full("ops/uw_w"))
+            otol = 1e-12 if g.prec == 64 else 1e-6
+            for hh, nm in zip(H, ("conv_wx", "conv_wy", "conv_wz")):
+                full = g.full("ops/" + nm)
+                e = float(np.linalg.norm((hh[ii] - full[ii]).ravel()) / np.linalg.norm(full.ravel())); worst = max(worst, e / otol)
+                if e >= otol:
+                    print(f"[rank {rank}] {case} convolution {nm}: {e:.2e} >= {otol}", flush=True); sys.exit(1)
+            after = ch.scalars()
+            if after["umax"] != before["umax"] or after["utau"] != before["utau"] or after["dt_next"] != before["dt_next"]:
+                print(f"[rank {rank}] {case} chan_convolution changed the step scalars", flush=True); sys.exit(1)
         ch.close()
     dist.barrier()
     print(f"[rank {rank}/{size}] multi-GPU parity OK (worst error/tolerance {worst:.2e})", flush=True)
