@@ -5,6 +5,9 @@
 # baseline ("--impl reference"); nothing here is linked into the product.
 #
 #   oracle/build_ref.sh NX NY NZ [32|64] [REYNOLDS]
+#   SHIM=1 oracle/build_ref.sh NX NY NZ [32|64]      the reference's DRIVER (RK3.c, RK3_kernels.cu, nonLinear.c,
+#        meanUevol.c, statistics.cu, fft.c, ...) linked against host/channel_shim.cu + libchannel_b200.so instead of its
+#        own operator files -> oracle/_ref/refshim_<grid>_f<prec>: the drop-in boundary as a program
 #
 # Grid sizes are compile-time macros in the reference (channel.h:42-44,
 # Makefile:8-11), hence one binary per grid.  No reference source is copied
@@ -38,6 +41,9 @@ FILES="RK3.c RK3_kernels.cu nonLinear.c nonLinear_kernels.cu convolution.c convo
 dealias.cu fft.c channel_cuda_mpi.c derivatives_nu_double.cu hemholzt_nu_double.cu
 implicitStep_nu_double.cu bilplacSolver_double.cu meanUevol.c statistics.cu imposeSymetry.c
 setUp.c check.cu"
+SHIM=${SHIM:-0}
+# the hybrid keeps the reference's driver and plumbing; its nine operator files are replaced by host/channel_shim.cu
+[ "$SHIM" = 1 ] && FILES="RK3.c RK3_kernels.cu nonLinear.c fft.c channel_cuda_mpi.c meanUevol.c statistics.cu setUp.c check.cu"
 
 patch_common() {
   sed -E \
@@ -90,9 +96,9 @@ for f in $FILES; do
   patch_common < "$TMP/$f.p" | retype > "$TMP/${f%.*}.cu"
   rm "$TMP/$f.p"
 done
-# P8 must have hit the 14 live launch sites at least
+# P8 must have hit the 14 live launch sites at least (the hybrid keeps 3 of them)
 n8=$(cat "$TMP"/*.cu | grep -c -- '-1)/threadsPerBlock' || true)
-[ "$n8" -ge 28 ] || { echo "P8 applied to $n8 lines only"; exit 1; }
+[ "$n8" -ge $([ "$SHIM" = 1 ] && echo 6 || echo 28) ] || { echo "P8 applied to $n8 lines only"; exit 1; }
 
 DEFS="-DNX=$NXv -DNY=$NYv -DNZ=$NZv -DREF_REYNOLDS=$RE"
 [ "$PREC" = 64 ] && DEFS="$DEFS -DREF_DOUBLE"
@@ -107,6 +113,18 @@ done
 wait
 $NVCC -O3 -w -gencode arch=compute_100a,code=sm_100a $DEFS -I"$HERE/stubs" -I"$TMP" \
       -include "$HERE/ref_shim.h" -c "$HERE/ref_harness.cu" -o "$TMP/ref_harness.o"
-BIN="$OUT/ref_${NXv}x${NYv}x${NZv}_f${PREC}"
-$NVCC -gencode arch=compute_100a,code=sm_100a -o "$BIN" $OBJS "$TMP/ref_harness.o" -lcufft -lcusparse -lcublas
+if [ "$SHIM" = 1 ]; then
+  LIBDIR=$HERE/../channel_gpu_b200/lib
+  [ -f "$LIBDIR/libchannel_b200.so" ] || { echo "build libchannel_b200.so first (python -m channel_gpu_b200.build)"; exit 1; }
+  retype < "$HERE/../host/channel_shim.cu" > "$TMP/channel_shim.cu"
+  $NVCC -O3 -w -gencode arch=compute_100a,code=sm_100a $DEFS -I"$HERE/stubs" -I"$TMP" -I"$HERE/../include" \
+        -include "$HERE/ref_shim.h" -c "$TMP/channel_shim.cu" -o "$TMP/channel_shim.o"
+  BIN="$OUT/refshim_${NXv}x${NYv}x${NZv}_f${PREC}"
+  # the binary finds the library relative to itself: the repository travels to the GPU box under another path
+  $NVCC -gencode arch=compute_100a,code=sm_100a -o "$BIN" $OBJS "$TMP/ref_harness.o" "$TMP/channel_shim.o" \
+        -L"$LIBDIR" -lchannel_b200 -Xlinker -rpath -Xlinker '$ORIGIN/../../channel_gpu_b200/lib' -lcufft -lcusparse -lcublas
+else
+  BIN="$OUT/ref_${NXv}x${NYv}x${NZv}_f${PREC}"
+  $NVCC -gencode arch=compute_100a,code=sm_100a -o "$BIN" $OBJS "$TMP/ref_harness.o" -lcufft -lcusparse -lcublas
+fi
 echo "built $BIN"
