@@ -359,6 +359,9 @@ def main():
         t = ms[sid] / nsub
         stages[name] = {"ms_per_substep": t, "launches_per_substep": cnt[sid] / nsub, "alg_GB_per_substep": nbytes / 1e9,
                         "GBps": nbytes / 1e6 / t if t > 0 else None, "frac_of_hbm_peak": nbytes / 1e6 / t / peak if t > 0 else None}
+    if world > 1:
+        stages["peer_copy_out"] = {"ms_per_substep": ms[8] / nsub, "note": "pencil -> plane: 6 fields, bulk NVLink copies (inside pencil_pre's time)"}
+        stages["peer_copy_back"] = {"ms_per_substep": ms[9] / nsub, "note": "plane -> pencil: 3 fields (inside plane_stage_total)"}
     stages["scalar"] = {"ms_per_substep": ms[2] / nsub, "note": "side stream, beside pencil_post"}
     stages["plane_stage_total"] = {"ms_per_substep": ms[1] / nsub, "note": "xfft_inv + zstage + xfft_fwd + (N>1) the exchange barriers"}
     stages["residual_ms_per_step"] = step_ms - 3 * (ms[0] + ms[1] + ms[3]) / nsub
@@ -423,12 +426,14 @@ def main():
     if world > 1:
         S = world
         xbytes = 9 * (P) * (S - 1) / S                      # per GPU per substep, each way (only active modes cross the wire)
-        xtime = stages["pencil_pre"]["ms_per_substep"] + stages["xfft_fwd"]["ms_per_substep"]
+        xtime = stages["peer_copy_out"]["ms_per_substep"] + stages["peer_copy_back"]["ms_per_substep"]
+        if xtime <= 0:                                      # in-kernel stores (CHAN_TUNE_PRE_DIRECT / FWD_DIRECT): charge the producing kernels
+            xtime = stages["pencil_pre"]["ms_per_substep"] + stages["xfft_fwd"]["ms_per_substep"]
         out["nvlink"] = {"bytes_per_gpu_per_step_each_way": int(3 * xbytes),
                          "achieved_GBps": xbytes / 1e6 / xtime if xtime > 0 else None, "peak_GBps": 900.0,
                          "frac": xbytes / 1e6 / xtime / 900.0 if xtime > 0 else None,
-                         "note": "bytes delivered per substep / (pencil_pre + xfft_fwd time): the two kernels whose stores ARE the exchange; they also do their own arithmetic, so this is a lower bound of the wire rate",
-                         "exchange": "NCCL grouped send/recv" if os.environ.get("CHAN_PEER", "1") == "0" else "peer stores over NVLink from pencil_pre / xfft_fwd (CUDA IPC) + 2 stream-ordered barriers per substep"}
+                         "note": "bytes leaving a GPU per substep / device time of the two bulk peer-copy kernels (CUDA events); the copies include the 1/N local part, which does not cross the wire and is not counted",
+                         "exchange": "NCCL grouped send/recv" if os.environ.get("CHAN_PEER", "1") == "0" else "bulk peer copies over NVLink (CUDA IPC mappings, destinations rotated by rank) + 2 stream-ordered barriers per substep"}
         out["parity_vs_golden"] = {"worst_error_over_tolerance": parity, "case": "64x21x9 fp64, 2 steps vs the reference build's dump (tests/golden), tolerance 1e-11, max over ranks and fields",
                                    "ok": bool(parity is not None and parity < 1.0)}
         out["reference_arm_note"] = "--impl reference runs ONE rank on one GPU at every N (see its config.note): the N>1 ratio is N GPUs against one"

@@ -276,8 +276,8 @@ class Channel:
         self._ck(self.L.chan_set_timing(self.h, int(bool(on))), "chan_set_timing")
 
     def stage_ms(self):
-        """Accumulated device milliseconds and counts per stage (pre, planes, scalar, post, whole step, xfft_inv, zstage, xfft_fwd) since the last call."""
-        ms = (C.c_double * 8)(); cnt = (C.c_long * 8)()
+        """Accumulated device milliseconds and counts per stage (pre, planes, scalar, post, whole step, xfft_inv, zstage, xfft_fwd, peer copies out, peer copies back) since the last call."""
+        ms = (C.c_double * 10)(); cnt = (C.c_long * 10)()
         self._ck(self.L.chan_get_stage_ms(self.h, ms, cnt), "chan_get_stage_ms")
         return list(ms), list(cnt)
 

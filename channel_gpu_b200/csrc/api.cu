@@ -84,7 +84,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1, false },
       { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1, false },
       { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1, false },
-      { "CHAN_TUNE_PRE_SCATTER", &h->tune.pre_scatter, 0, false },
+      { "CHAN_TUNE_PRE_DIRECT", &h->tune.pre_direct, 0, false },
+      { "CHAN_TUNE_FWD_DIRECT", &h->tune.fwd_direct, 0, false },
       { "CHAN_TUNE_LANES", &h->tune.lanes, -1, false },
       { "CHAN_TUNE_LANES_S", &h->tune.lanes_s, 4, false },
       { "CHAN_TUNE_LANES_MB", &h->tune.lanes_mb, 0, false },
@@ -173,12 +174,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // to fill the GPU with one thread per chain (small grids, many GPUs).
   // y stage: thread-per-chain kernels (batched row loads, HBM-bound) when there are enough chains to fill the
   // SMs, the segment-parallel register kernels when a rank holds few chains (many ranks / small grids)
-  // `pre`: the register kernel below 148*256 chains, and always when there are several GPUs - the thread-per-chain
-  // kernel walks the rows in order, so all ranks store into the SAME plane owner at the same time (measured at
-  // Re_tau=1000 on 8 GPUs: 3.1 ms per substep for 1/8 of the chains, as much as one GPU needs for all of them);
-  // the register kernel has every row in flight at once.
+  // `pre`: the register kernel below 148*256 chains.  With several GPUs the kernels store locally and a bulk scatter
+  // delivers the rows (kernels_pencil.cu: launch_peer_scatter); with CHAN_TUNE_PRE_DIRECT=1 they store straight into the
+  // plane owners' buffers, and then the register kernel is forced: the thread-per-chain kernel walks the rows in order, so
+  // all ranks would store into the SAME plane owner at the same time (Re_tau=1000 on 8 GPUs: 3.1 ms per substep).
   // `post`: the chain kernels win at every size measured.
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || cfg->size > 1) ? 1 : 0;
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || (cfg->size > 1 && h->tune.pre_direct)) ? 1 : 0;
   if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   // on-chip y stage (warps per mode, lanes along y; kernels_pencil_lanes.cu): bit 0 = post, bit 1 = pre.  It needs a
@@ -484,6 +485,11 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   t = t_begin(h, CHAN_STAGE_PRE);
   if ((rc = (h->tune.lanes & 2) ? launch_pencil_pre_lanes(h)
           : ((h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h)))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
+  if (h->peer_ready && !h->tune.pre_direct) {                                                          // pencil -> plane transpose over NVLink
+    int t2 = t_begin(h, CHAN_STAGE_XCHG_OUT);
+    if ((rc = launch_peer_scatter(h))) return rc;
+    t_end(h, t2);
+  }
   t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
   t_end(h, t);

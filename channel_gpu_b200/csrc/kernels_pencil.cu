@@ -373,21 +373,67 @@ __global__ void __launch_bounds__(128, 4) pencil_pre_kernel(PArgs<T> a, PeerOut 
   }
 }
 
-// delivery of the six plane-stage inputs of row j (u, v, w, omega) to the rank that owns plane j; one thread per
-// complex element, every row in flight at once so that the stores spread over all destinations
-template <typename T>
-__global__ void __launch_bounds__(256) peer_scatter_kernel(PArgs<T> a, PeerOut po) {
-  typedef typename Vec2<T>::type T2;
-  const long m = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = blockIdx.y;
-  if (m >= a.M) return;
-  int p = 0;
+// Delivery of the six plane-stage inputs (u, v, w, omega) to the plane owners over NVLink: the pencil -> plane
+// transpose of channel_cuda_mpi.c:95-128.  In the plane-major layout the rows a peer needs are ONE contiguous slab of
+// each field (rows [j0_p, j0_p + nyl_p) x all local modes), so the delivery is 6 x S flat copies.  Two things decide its
+// speed (measured on 8 B200s, profiles/r02_n8_notes.txt): the packets must be large — stores issued from inside the y
+// kernels are 64..128-byte row pieces and reach 240-330 GB/s per GPU — and no two ranks may send to the same owner at
+// the same time: block z of rank r copies to rank (r + z) mod S, so the ranks walk the destinations in step, one sender
+// per receiver at any moment.
+struct ScatterArgs { const void* src[6]; void* dst[8][6]; long src_off[8], dst_off[8], count[8]; int S, rank; };
+template <typename V>
+__global__ void __launch_bounds__(256) peer_scatter_kernel(ScatterArgs a) {
+  const int p = (a.rank + blockIdx.z) % a.S, q = blockIdx.y;
+  const V* __restrict__ s = (const V*)a.src[q] + a.src_off[p];
+  V* __restrict__ d = (V*)a.dst[p][q] + a.dst_off[p];
+  const long n = a.count[p], stride = (long)gridDim.x * blockDim.x * 4;
+  for (long i0 = (long)blockIdx.x * blockDim.x * 4 + threadIdx.x; i0 < n; i0 += stride) {
+    V v[4];
 #pragma unroll
-  for (int i = 1; i < 8; i++) p += (i < po.nranks && j >= po.part_j[i]) ? 1 : 0;
-  const long src = (long)j * a.M + m, dst = po.src_off[p] + (long)(j - po.part_j[p]) * a.M + m;
-  const T2* f[6] = { a.u, a.v, a.w, a.ox, a.oy, a.oz };
+    for (int k = 0; k < 4; k++) { const long i = i0 + (long)k * blockDim.x; if (i < n) v[k] = s[i]; }
 #pragma unroll
-  for (int q = 0; q < 6; q++) ((T2*)po.rcv[p][q])[dst] = f[q][src];
+    for (int k = 0; k < 4; k++) { const long i = i0 + (long)k * blockDim.x; if (i < n) d[i] = v[k]; }
+  }
+}
+static int run_scatter(chan_handle* h, ScatterArgs& a, int nf) {
+  const int S = h->cfg.size;
+  a.S = S; a.rank = h->cfg.rank;
+  // copy units of 16 bytes: one fp64 complex, or two fp32 complex when every offset and count is even
+  const long per16 = h->prec == 8 ? 1 : 2;
+  bool even = true;
+  for (int p = 0; p < S; p++) if ((a.src_off[p] | a.dst_off[p] | a.count[p]) % per16) even = false;
+  dim3 grid(16, nf, S);
+  if (h->prec == 8) peer_scatter_kernel<double2><<<grid, 256, 0, h->stream>>>(a);
+  else if (even) { for (int p = 0; p < S; p++) { a.src_off[p] /= 2; a.dst_off[p] /= 2; a.count[p] /= 2; } peer_scatter_kernel<float4><<<grid, 256, 0, h->stream>>>(a); }
+  else peer_scatter_kernel<float2><<<grid, 256, 0, h->stream>>>(a);
+  h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+int launch_peer_scatter(chan_handle* h) {
+  ScatterArgs a; memset(&a, 0, sizeof(a));
+  const void* f[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
+  const long M = h->d.M;
+  for (int q = 0; q < 6; q++) a.src[q] = f[q];
+  for (int p = 0; p < h->cfg.size; p++) {
+    const long nyl = h->part_j[p + 1] - h->part_j[p];
+    a.src_off[p] = (long)h->part_j[p] * M; a.dst_off[p] = nyl * h->d.ikx0 * h->d.Kz; a.count[p] = nyl * M;
+    for (int q = 0; q < 6; q++) a.dst[p][q] = h->peer_rcv[p][q];
+  }
+  return run_scatter(h, a, 6);
+}
+// The way back (transposeXYZ2YZX, channel_cuda_mpi.c:64-93): xfft_fwd leaves the three products in the plane-side send
+// buffers, one block per destination rank (SegMap), and each block is one contiguous slab [j0, j0+nyl) x (all modes of the
+// destination) of the destination's pencil-side field.
+int launch_peer_scatter_back(chan_handle* h) {
+  ScatterArgs a; memset(&a, 0, sizeof(a));
+  for (int q = 0; q < 3; q++) a.src[q] = h->snd[q];
+  for (int p = 0; p < h->cfg.size; p++) {
+    const long Mp = (long)h->seg.width[p] * h->d.Kz;
+    a.src_off[p] = h->seg.base[p]; a.dst_off[p] = (long)h->d.j0 * Mp; a.count[p] = (long)h->d.nyl * Mp;
+    for (int q = 0; q < 3; q++) a.dst[p][q] = h->peer_H[p][q];
+  }
+  return run_scatter(h, a, 3);
 }
 
 // =================================================================================
@@ -774,18 +820,6 @@ static int pre_t(chan_handle* h) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   long nchain = 2 * h->d.M;
   PeerOut po; fill_peer_out(h, po);
-  if (po.nranks > 1 && h->tune.pre_scatter) {
-    // experiment (CHAN_TUNE_PRE_SCATTER=1 with CHAN_TUNE_PENCIL_SEG=0): the chain kernel walks the rows in order, so
-    // its peer stores hit one plane owner at a time ("Incast"); store locally instead and let a
-    // kernel with every row in flight deliver the six fields
-    PeerOut local; memset(&local, 0, sizeof(local)); local.nranks = 1;
-    pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, local);
-    dim3 grid((unsigned)((h->d.M + 255) / 256), (unsigned)h->d.ny);
-    peer_scatter_kernel<T><<<grid, 256, 0, h->stream>>>(a, po);
-    h->launches += 2;
-    CHAN_CUDA(h, cudaGetLastError());
-    return CHAN_OK;
-  }
   pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, po);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());

@@ -273,9 +273,13 @@ __device__ __forceinline__ void var_lanes(LCtx& c, const LaneTabs& t, const doub
 
 // the six functions of setBoundaryCond (bilplacSolver_double.cu:174-217) at one y; same expressions as bc_functions
 // (pencil_common.cuh), all four exponentials evaluated here (re and im of a mode share the result)
+// exp / expf of arguments far below their underflow thresholds (-745.2 / -103.97) return exactly 0: skip the call there.
+// l1 = sqrt(kk + Re/(dt beta)) is in the thousands, so away from the walls a whole warp takes the short way.
+__device__ __forceinline__ double exp_or_zero(double x) { return x < -760.0 ? 0.0 : exp(x); }
+__device__ __forceinline__ double expf_or_zero(double x) { return x < -110.0 ? 0.0 : (double)expf((float)x); }
 __device__ __forceinline__ BcFun bc_functions_all(const BcCoef& k, double y) {
-  const double E1m = (double)expf((float)(-k.l1 * (1.0 - y))), E1p = exp(-k.l1 * (1.0 + y));
-  const double E2m = (double)expf((float)(-k.l2 * (1.0 - y))), E2p = exp(-k.l2 * (1.0 + y));
+  const double E1m = expf_or_zero(-k.l1 * (1.0 - y)), E1p = exp_or_zero(-k.l1 * (1.0 + y));
+  const double E2m = expf_or_zero(-k.l2 * (1.0 - y)), E2p = exp_or_zero(-k.l2 * (1.0 + y));
   const double a1 = (E1m + E1p) * k.ip1, b1 = (E1m - E1p) * k.im1, a1d = (E1m - E1p) * k.ip1, b1d = (E1m + E1p) * k.im1;
   const double a2 = (E2m + E1p) * k.ip2, b2 = (E2m - E2p) * k.im2, a2d = (E2m - E1p) * k.ip2, b2d = (E2m + E2p) * k.im2;
   const double hD = 0.5 * k.D;

@@ -272,7 +272,8 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
   for (int f = 0; f < 6; f++) xi.src[f] = (const T2*)(multi ? h->rcv[f] : pin[f]);
   for (int f = 0; f < 3; f++) for (int g = 0; g < 8; g++) xf.dst[f].p[g] = (T2*)(multi ? h->snd[f] : pout[f]);
-  if (peer) peer_out<T>(h, xf);
+  const bool direct = peer && h->tune.fwd_direct;          // stores of xfft_fwd go straight into the pencil owners' fields (64-byte pieces)
+  if (direct) peer_out<T>(h, xf);
   ZArgs<T> z; fill_z(h, z);
   if (op_level) z.umax_bits = h->sc->umax_scratch;         // the reference's convolution() does not touch calcDt's maxima
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
@@ -284,6 +285,11 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
     rc = launch_z<T, ZM_ROTOR>(h, z, 6, pb); if (rc) return rc;
     timing_end(h, t); t = timing_begin(h, CHAN_STAGE_XFWD);
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
+    timing_end(h, t);
+  }
+  if (peer && !direct) {                                                       // plane -> pencil transpose as bulk peer copies
+    int t = timing_begin(h, CHAN_STAGE_XCHG_BACK);
+    int rc = launch_peer_scatter_back(h); if (rc) return rc;
     timing_end(h, t);
   }
   if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer stores

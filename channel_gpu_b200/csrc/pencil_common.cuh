@@ -133,11 +133,12 @@ __device__ __forceinline__ void uw_comp(const Wave<T>& wv, const Mode& md, bool 
 template <typename T>
 void fill_pencil_args(chan_handle* h, PArgs<T>& a);
 
-// where the `pre` kernels deliver their rows: locally, or straight into the plane owners' receive buffers
+// where the `pre` kernels deliver their rows: locally (a bulk scatter follows when there are several GPUs, the default), or
+// straight into the plane owners' receive buffers from inside the kernel (CHAN_TUNE_PRE_DIRECT=1: small packets, slower)
 static inline void fill_peer_out(chan_handle* h, PeerOut& po) {
   memset(&po, 0, sizeof(po));
-  po.nranks = h->peer_ready ? h->cfg.size : 1;
-  if (!h->peer_ready) return;
+  po.nranks = (h->peer_ready && h->tune.pre_direct) ? h->cfg.size : 1;
+  if (po.nranks == 1) return;
   for (int p = 0; p <= h->cfg.size; p++) po.part_j[p] = h->part_j[p];
   for (int p = 0; p < h->cfg.size; p++) {
     po.src_off[p] = (long)(h->part_j[p + 1] - h->part_j[p]) * h->d.ikx0 * h->d.Kz;

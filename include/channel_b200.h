@@ -87,14 +87,15 @@ long chan_launch_count(const chan_handle* h);   /* kernels launched so far */
  * counterpart in the reference, which has no timers at all).  Stages:
  * 0 pencil_pre, 1 plane stage (x/z FFTs + u x omega), 2 scalar stage, 3 pencil_post,
  * 4 one whole RK3 step as issued by chan_rk_step (encloses the others);
- * 5 xfft_inv, 6 zstage, 7 xfft_fwd: the three kernels inside stage 1.
+ * 5 xfft_inv, 6 zstage, 7 xfft_fwd: the three kernels inside stage 1;
+ * 8, 9 (several GPUs): the bulk peer copies pencil -> plane (inside stage 0) and plane -> pencil (inside stage 1).
  * chan_get_stage_ms synchronises, returns accumulated milliseconds and launch
- * groups per stage since the last call, and resets them.  At most 1024 stage
+ * groups per stage (arrays of CHAN_STAGE_COUNT) since the last call, and resets them.  At most 1024 stage
  * instances are recorded between two reads; later ones are not timed. */
 enum { CHAN_STAGE_PRE = 0, CHAN_STAGE_PLANES, CHAN_STAGE_SCALAR, CHAN_STAGE_POST, CHAN_STAGE_STEP,
-       CHAN_STAGE_XINV, CHAN_STAGE_Z, CHAN_STAGE_XFWD, CHAN_STAGE_COUNT };
+       CHAN_STAGE_XINV, CHAN_STAGE_Z, CHAN_STAGE_XFWD, CHAN_STAGE_XCHG_OUT, CHAN_STAGE_XCHG_BACK, CHAN_STAGE_COUNT };
 int  chan_set_timing(chan_handle* h, int on);
-int  chan_get_stage_ms(chan_handle* h, double* ms_out8, long* count_out8);
+int  chan_get_stage_ms(chan_handle* h, double* ms_out, long* count_out);
 
 /* ---- state in/out, HOST pointers, reference layout ------------------------- */
 /* readData / genRandData + cudaMemcpy H2D (io.c:3-34,74-98; main.c:107-114) */
