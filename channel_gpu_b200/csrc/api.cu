@@ -132,6 +132,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     CHAN_CUDA(h, cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, hi));
   }
+  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xs, cudaStreamNonBlocking));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_xs, cudaEventDisableTiming));
+  for (int i = 0; i < 64; i++) CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   int rc;
@@ -150,6 +153,9 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   int pb = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(1536u << 20) / plane_q);
   if (pb < 1) pb = 1;
   if (pb > d.nyl) pb = d.nyl;
+  // several GPUs: at least four batches (of at least four planes), so that the peer copies of one batch overlap the
+  // transforms of the next (kernels_plane.cu)
+  if (cfg->size > 1 && cfg->plane_batch <= 0) { int q = (d.nyl + 3) / 4; if (q < 4) q = 4; if (pb > q) pb = q; }
   h->plane_batch = pb;
   if ((rc = alloc_dev(h, &h->Q, plane_q * pb))) return rc;
   if (cfg->size > 1) {
@@ -206,6 +212,9 @@ extern "C" void chan_destroy(chan_handle* h) {
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
+  for (int i = 0; i < 64; i++) if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]);
+  if (h->ev_xs) cudaEventDestroy(h->ev_xs);
+  if (h->xs) cudaStreamDestroy(h->xs);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->aux) cudaStreamDestroy(h->aux);

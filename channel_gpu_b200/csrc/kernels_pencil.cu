@@ -425,12 +425,13 @@ int launch_peer_scatter(chan_handle* h) {
 // The way back (transposeXYZ2YZX, channel_cuda_mpi.c:64-93): xfft_fwd leaves the three products in the plane-side send
 // buffers, one block per destination rank (SegMap), and each block is one contiguous slab [j0, j0+nyl) x (all modes of the
 // destination) of the destination's pencil-side field.
-int launch_peer_scatter_back(chan_handle* h) {
+// rows [js, js+pb) of this rank's planes (one plane batch), on h->stream
+int launch_peer_scatter_back(chan_handle* h, int js, int pb) {
   ScatterArgs a; memset(&a, 0, sizeof(a));
   for (int q = 0; q < 3; q++) a.src[q] = h->snd[q];
   for (int p = 0; p < h->cfg.size; p++) {
     const long Mp = (long)h->seg.width[p] * h->d.Kz;
-    a.src_off[p] = h->seg.base[p]; a.dst_off[p] = (long)h->d.j0 * Mp; a.count[p] = (long)h->d.nyl * Mp;
+    a.src_off[p] = h->seg.base[p] + (long)js * Mp; a.dst_off[p] = (long)(h->d.j0 + js) * Mp; a.count[p] = (long)pb * Mp;
     for (int q = 0; q < 3; q++) a.dst[p][q] = h->peer_H[p][q];
   }
   return run_scatter(h, a, 3);

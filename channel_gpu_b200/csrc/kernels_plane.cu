@@ -286,12 +286,20 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
     timing_end(h, t); t = timing_begin(h, CHAN_STAGE_XFWD);
     rc = launch_x_any<T>(h, false, xf, 3, pb); if (rc) return rc;
     timing_end(h, t);
+    if (peer && !direct) {
+      // plane -> pencil transpose as bulk peer copies, batch by batch on a side stream: the products of this batch cross
+      // NVLink while the next batch is being transformed
+      const int ib = js / h->plane_batch;
+      cudaStream_t main_stream = h->stream;
+      if (ib < 64) { CHAN_CUDA(h, cudaEventRecord(h->ev_batch[ib], main_stream)); CHAN_CUDA(h, cudaStreamWaitEvent(h->xs, h->ev_batch[ib], 0)); h->stream = h->xs; }
+      t = timing_begin(h, CHAN_STAGE_XCHG_BACK);
+      rc = launch_peer_scatter_back(h, js, pb);
+      timing_end(h, t);
+      h->stream = main_stream;
+      if (rc) return rc;
+    }
   }
-  if (peer && !direct) {                                                       // plane -> pencil transpose as bulk peer copies
-    int t = timing_begin(h, CHAN_STAGE_XCHG_BACK);
-    int rc = launch_peer_scatter_back(h); if (rc) return rc;
-    timing_end(h, t);
-  }
+  if (peer && !direct) { CHAN_CUDA(h, cudaEventRecord(h->ev_xs, h->xs)); CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_xs, 0)); }
   if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer stores
   if (multi && !peer) { int rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
   return CHAN_OK;
