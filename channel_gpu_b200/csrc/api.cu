@@ -133,8 +133,10 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, hi));
   }
   CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xs, cudaStreamNonBlocking));
+  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xo, cudaStreamNonBlocking));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_xs, cudaEventDisableTiming));
-  for (int i = 0; i < 64; i++) CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_pre, cudaEventDisableTiming));
+  for (int i = 0; i < 64; i++) { CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)); }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   int rc;
@@ -150,12 +152,19 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // launches win over L2 residency of the staging, so take as many planes per launch group as fit in
   // 1.5 GiB of staging (all of them up to Re_tau=550; 10 at Re_tau=1000 in fp64)
   const size_t plane_q = (size_t)6 * d.nx * d.Kz * csize(h);
-  int pb = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(1536u << 20) / plane_q);
-  if (pb < 1) pb = 1;
-  if (pb > d.nyl) pb = d.nyl;
-  // several GPUs: at least four batches (of at least four planes), so that the peer copies of one batch overlap the
-  // transforms of the next (kernels_plane.cu)
-  if (cfg->size > 1 && cfg->plane_batch <= 0) { int q = (d.nyl + 3) / 4; if (q < 4) q = 4; if (pb > q) pb = q; }
+  h->nbatch = 1;
+  for (int r = 0; r < cfg->size; r++) {      // the same arithmetic on every rank: senders address the batches of their peers
+    const int nyl_r = h->part_j[r + 1] - h->part_j[r];
+    int pbr = cfg->plane_batch > 0 ? cfg->plane_batch : (int)((size_t)(1536u << 20) / plane_q);
+    if (pbr < 1) pbr = 1;
+    if (pbr > nyl_r) pbr = nyl_r;
+    // several GPUs: at least four batches (of at least four planes), so that the peer copies of one batch overlap the
+    // transforms of the next (kernels_plane.cu)
+    if (cfg->size > 1 && cfg->plane_batch <= 0) { int q = (nyl_r + 3) / 4; if (q < 4) q = 4; if (pbr > q) pbr = q; }
+    h->pb_rank[r] = pbr;
+    const int nb = (nyl_r + pbr - 1) / pbr; if (nb > h->nbatch) h->nbatch = nb;
+  }
+  const int pb = h->pb_rank[cfg->rank];
   h->plane_batch = pb;
   if ((rc = alloc_dev(h, &h->Q, plane_q * pb))) return rc;
   if (cfg->size > 1) {
@@ -212,9 +221,11 @@ extern "C" void chan_destroy(chan_handle* h) {
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
-  for (int i = 0; i < 64; i++) if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]);
+  for (int i = 0; i < 64; i++) { if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]); if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]); }
   if (h->ev_xs) cudaEventDestroy(h->ev_xs);
+  if (h->ev_pre) cudaEventDestroy(h->ev_pre);
   if (h->xs) cudaStreamDestroy(h->xs);
+  if (h->xo) cudaStreamDestroy(h->xo);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->aux) cudaStreamDestroy(h->aux);
@@ -494,12 +505,31 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   t = t_begin(h, CHAN_STAGE_PRE);
   if ((rc = (h->tune.lanes & 2) ? launch_pencil_pre_lanes(h)
           : ((h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h)))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
-  if (h->peer_ready && !h->tune.pre_direct) {                                                          // pencil -> plane transpose over NVLink
+  t_end(h, t);
+  if (h->peer_ready && !h->tune.pre_direct && h->tune.fwd_direct) {          // all rows at once, the plane stage waits for everything
     int t2 = t_begin(h, CHAN_STAGE_XCHG_OUT);
-    if ((rc = launch_peer_scatter(h))) return rc;
+    if ((rc = launch_peer_scatter(h, -1))) return rc;
     t_end(h, t2);
+  } else if (h->peer_ready && !h->tune.pre_direct) {
+    // pencil -> plane transpose over NVLink, one bulk copy kernel per plane batch of the destinations on a side stream, each
+    // followed by a stream-ordered barrier of all ranks: the plane stage of batch b starts as soon as batch b has arrived
+    // everywhere, while the rows of the later batches are still travelling
+    if (h->nbatch > 64) return set_err(h, CHAN_ERR_ARG, "more than 64 plane batches per rank");
+    cudaStream_t main_stream = h->stream;
+    CHAN_CUDA(h, cudaEventRecord(h->ev_pre, main_stream));
+    CHAN_CUDA(h, cudaStreamWaitEvent(h->xo, h->ev_pre, 0));
+    h->stream = h->xo;
+    for (int b = 0; b < h->nbatch && !rc; b++) {
+      int t2 = t_begin(h, CHAN_STAGE_XCHG_OUT);
+      rc = launch_peer_scatter(h, b);
+      t_end(h, t2);
+      if (!rc) rc = stream_barrier(h);
+      if (!rc && cudaEventRecord(h->ev_in[b], h->xo) != cudaSuccess) rc = set_err(h, CHAN_ERR_CUDA, "event record failed");
+    }
+    h->stream = main_stream;
+    if (rc) return rc;
   }
-  t_end(h, t); t = t_begin(h, CHAN_STAGE_PLANES);
+  t = t_begin(h, CHAN_STAGE_PLANES);
   if ((rc = launch_nonlinear_planes(h))) return rc;       // 6 C2R, u x omega, 3 R2C, truncation
   t_end(h, t);
   // The mean-flow / dt kernel is one block of serial work and shares nothing with pencil_post (it reads

@@ -99,7 +99,9 @@ struct chan_handle {
   cudaStream_t stream;
   cudaStream_t aux;             // side stream: the one-block mean-flow/dt kernel runs beside pencil_post
   cudaStream_t xs;              // side stream of the plane -> pencil peer copies: batch b travels while batch b+1 is transformed
-  cudaEvent_t ev_batch[64], ev_xs;
+  cudaStream_t xo;              // side stream of the pencil -> plane peer copies: the rows of plane batch b+1 travel while batch b is transformed
+  cudaEvent_t ev_batch[64], ev_in[64], ev_xs, ev_pre;
+  int pb_rank[8], nbatch;       // plane batch of every rank (same formula everywhere) and the largest batch count of any rank
   cudaEvent_t ev_fork, ev_join;
   // state + work fields, compact plane-major, complex T
   void *phi, *g, *v, *dv, *Rphi, *Rg;
@@ -164,7 +166,7 @@ int perm_pos_of(const FftPlan& p, int n);
 int launch_pencil_pre(chan_handle* h);
 int launch_pencil_post(chan_handle* h, int n);
 int launch_peer_scatter_back(chan_handle* h, int js, int pb);     // the three products -> the pencil owners
-int launch_peer_scatter(chan_handle* h);          // the six plane-stage inputs -> the plane owners (bulk peer copies)
+int launch_peer_scatter(chan_handle* h, int batch);   // batch b of every destination; -1: everything          // the six plane-stage inputs -> the plane owners (bulk peer copies)
 int launch_op(chan_handle* h, int op, void* f0, void* f1, void* f2, double betha, double dt);
 // kernels_pencil_seg.cu
 int seg_supported(chan_handle* h);

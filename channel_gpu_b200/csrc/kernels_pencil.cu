@@ -410,14 +410,16 @@ static int run_scatter(chan_handle* h, ScatterArgs& a, int nf) {
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
 }
-int launch_peer_scatter(chan_handle* h) {
+int launch_peer_scatter(chan_handle* h, int batch) {
   ScatterArgs a; memset(&a, 0, sizeof(a));
   const void* f[6] = { h->u, h->v, h->w, h->ox, h->oy, h->oz };
   const long M = h->d.M;
   for (int q = 0; q < 6; q++) a.src[q] = f[q];
   for (int p = 0; p < h->cfg.size; p++) {
     const long nyl = h->part_j[p + 1] - h->part_j[p];
-    a.src_off[p] = (long)h->part_j[p] * M; a.dst_off[p] = nyl * h->d.ikx0 * h->d.Kz; a.count[p] = nyl * M;
+    long r0 = 0, nr = nyl;                                   // rows of the destination's plane batch `batch`
+    if (batch >= 0) { r0 = (long)batch * h->pb_rank[p]; nr = nyl - r0 < h->pb_rank[p] ? nyl - r0 : h->pb_rank[p]; if (nr < 0) nr = 0; if (r0 > nyl) r0 = nyl; }
+    a.src_off[p] = ((long)h->part_j[p] + r0) * M; a.dst_off[p] = nyl * h->d.ikx0 * h->d.Kz + r0 * M; a.count[p] = nr * M;
     for (int q = 0; q < 6; q++) a.dst[p][q] = h->peer_rcv[p][q];
   }
   return run_scatter(h, a, 6);

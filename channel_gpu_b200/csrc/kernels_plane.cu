@@ -268,7 +268,8 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   const bool multi = h->cfg.size > 1, peer = multi && h->peer_ready;
   // operator-level calls (chan_convolution) left their inputs in the LOCAL pencil fields: nothing has been
   // delivered to the plane owners, so the input side goes through the NCCL exchange even when peer stores are on
-  if (peer && !op_level) { int rc = stream_barrier(h); if (rc) return rc; }    // every rank's `pre` has delivered
+  const bool piped = peer && !op_level && !h->tune.pre_direct && !h->tune.fwd_direct;   // the inputs arrive batch by batch (chan_rk_substep)
+  if (peer && !op_level && !piped) { int rc = stream_barrier(h); if (rc) return rc; }    // every rank's `pre` has delivered
   else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
   for (int f = 0; f < 6; f++) xi.src[f] = (const T2*)(multi ? h->rcv[f] : pin[f]);
   for (int f = 0; f < 3; f++) for (int g = 0; g < 8; g++) xf.dst[f].p[g] = (T2*)(multi ? h->snd[f] : pout[f]);
@@ -279,6 +280,7 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   for (int js = 0; js < h->d.nyl; js += h->plane_batch) {
     int pb = h->d.nyl - js < h->plane_batch ? h->d.nyl - js : h->plane_batch;
     xi.j_start = xf.j_start = z.j_start = js; xi.pb = xf.pb = z.pb = pb;
+    if (piped) CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_in[js / h->plane_batch], 0));   // batch arrived from every rank
     int t = timing_begin(h, CHAN_STAGE_XINV);
     int rc = launch_x_any<T>(h, true, xi, 6, pb); if (rc) return rc;
     timing_end(h, t); t = timing_begin(h, CHAN_STAGE_Z);
@@ -291,7 +293,12 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
       // NVLink while the next batch is being transformed
       const int ib = js / h->plane_batch;
       cudaStream_t main_stream = h->stream;
-      if (ib < 64) { CHAN_CUDA(h, cudaEventRecord(h->ev_batch[ib], main_stream)); CHAN_CUDA(h, cudaStreamWaitEvent(h->xs, h->ev_batch[ib], 0)); h->stream = h->xs; }
+      if (ib < 64) {
+        CHAN_CUDA(h, cudaEventRecord(h->ev_batch[ib], main_stream)); CHAN_CUDA(h, cudaStreamWaitEvent(h->xs, h->ev_batch[ib], 0));
+        // the products of these planes land in the peers' omega fields, over the very rows the peers sent for THIS batch:
+        // their copies are complete (the barrier of batch ib preceded the transforms), later batches touch other rows
+        h->stream = h->xs;
+      }
       t = timing_begin(h, CHAN_STAGE_XCHG_BACK);
       rc = launch_peer_scatter_back(h, js, pb);
       timing_end(h, t);
@@ -299,6 +306,7 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
       if (rc) return rc;
     }
   }
+  if (piped) CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_in[h->nbatch - 1], 0));   // every outgoing copy of this rank is done: the next `pre` may overwrite its sources
   if (peer && !direct) { CHAN_CUDA(h, cudaEventRecord(h->ev_xs, h->xs)); CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_xs, 0)); }
   if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer stores
   if (multi && !peer) { int rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
