@@ -360,11 +360,11 @@ def main():
         stages[name] = {"ms_per_substep": t, "launches_per_substep": cnt[sid] / nsub, "alg_GB_per_substep": nbytes / 1e9,
                         "GBps": nbytes / 1e6 / t if t > 0 else None, "frac_of_hbm_peak": nbytes / 1e6 / t / peak if t > 0 else None}
     if world > 1:
-        stages["peer_copy_out"] = {"ms_per_substep": ms[8] / nsub, "note": "pencil -> plane: 6 fields, bulk NVLink copies (inside pencil_pre's time)"}
+        stages["peer_copy_out"] = {"ms_per_substep": ms[8] / nsub, "note": "pencil -> plane: 6 fields, bulk NVLink copies (between pencil_pre and the plane stage)"}
         stages["peer_copy_back"] = {"ms_per_substep": ms[9] / nsub, "note": "plane -> pencil: 3 fields (inside plane_stage_total)"}
     stages["scalar"] = {"ms_per_substep": ms[2] / nsub, "note": "side stream, beside pencil_post"}
     stages["plane_stage_total"] = {"ms_per_substep": ms[1] / nsub, "note": "xfft_inv + zstage + xfft_fwd + (N>1) the exchange barriers"}
-    stages["residual_ms_per_step"] = step_ms - 3 * (ms[0] + ms[1] + ms[3]) / nsub
+    stages["residual_ms_per_step"] = step_ms - 3 * (ms[0] + ms[1] + ms[3] + ms[8]) / nsub      # launch gaps, side-stream joins, the end-of-step kernel
     if args.profile:
         if rank == 0:
             print(json.dumps({"profile_run": True, "n_gpus": world, "ms_per_step": step_ms, "stage_ms": ms, "stage_cnt": cnt, "launches": launches, "stages": stages, "knobs": knobs}))

@@ -86,6 +86,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1, false },
       { "CHAN_TUNE_PRE_DIRECT", &h->tune.pre_direct, 0, false },
       { "CHAN_TUNE_FWD_DIRECT", &h->tune.fwd_direct, 0, false },
+      { "CHAN_TUNE_XCHG_PIPE", &h->tune.xchg_pipe, 0, false },
       { "CHAN_TUNE_LANES", &h->tune.lanes, -1, false },
       { "CHAN_TUNE_LANES_S", &h->tune.lanes_s, 4, false },
       { "CHAN_TUNE_LANES_MB", &h->tune.lanes_mb, 0, false },
@@ -132,8 +133,12 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     CHAN_CUDA(h, cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, hi));
   }
-  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xs, cudaStreamNonBlocking));
-  CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xo, cudaStreamNonBlocking));
+  {   // the peer-copy streams outrank the main stream: their few blocks must not queue behind the thousands of an FFT launch
+    int lo = 0, hi = 0;
+    CHAN_CUDA(h, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->xs, cudaStreamNonBlocking, hi));
+    CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->xo, cudaStreamNonBlocking, hi));
+  }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_xs, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_pre, cudaEventDisableTiming));
   for (int i = 0; i < 64; i++) { CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)); }
@@ -160,7 +165,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     if (pbr > nyl_r) pbr = nyl_r;
     // several GPUs: at least four batches (of at least four planes), so that the peer copies of one batch overlap the
     // transforms of the next (kernels_plane.cu)
-    if (cfg->size > 1 && cfg->plane_batch <= 0) { int q = (nyl_r + 3) / 4; if (q < 4) q = 4; if (pbr > q) pbr = q; }
+    if (cfg->size > 1 && cfg->plane_batch <= 0 && h->tune.xchg_pipe) { int q = (nyl_r + 3) / 4; if (q < 4) q = 4; if (pbr > q) pbr = q; }
     h->pb_rank[r] = pbr;
     const int nb = (nyl_r + pbr - 1) / pbr; if (nb > h->nbatch) h->nbatch = nb;
   }
@@ -506,11 +511,14 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if ((rc = (h->tune.lanes & 2) ? launch_pencil_pre_lanes(h)
           : ((h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h)))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
   t_end(h, t);
-  if (h->peer_ready && !h->tune.pre_direct && h->tune.fwd_direct) {          // all rows at once, the plane stage waits for everything
+  if (h->peer_ready && !h->tune.pre_direct && (h->tune.fwd_direct || !h->tune.xchg_pipe)) {          // all rows at once, the plane stage waits for everything
     int t2 = t_begin(h, CHAN_STAGE_XCHG_OUT);
     if ((rc = launch_peer_scatter(h, -1))) return rc;
     t_end(h, t2);
   } else if (h->peer_ready && !h->tune.pre_direct) {
+    // CHAN_TUNE_XCHG_PIPE=1, off by default: measured slower than the all-at-once copy on 2 and 8 GPUs (Re_tau=1000: 22.9 vs
+    // 18.3 ms per step on 8 GPUs, profiles/r02_n8_notes.txt) - the copies and the transforms slow each other down and the
+    // extra barriers cost more than the overlap hides.
     // pencil -> plane transpose over NVLink, one bulk copy kernel per plane batch of the destinations on a side stream, each
     // followed by a stream-ordered barrier of all ranks: the plane stage of batch b starts as soon as batch b has arrived
     // everywhere, while the rows of the later batches are still travelling

@@ -133,7 +133,7 @@ struct chan_handle {
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;   // the rank's slab [Kxl][NZ][NY] of the reference layout
   double* stat_buf;             // 4*NY sums of chan_statistics
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_direct, fwd_direct, lanes, lanes_s, lanes_mb; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_direct, fwd_direct, xchg_pipe, lanes, lanes_s, lanes_mb; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)

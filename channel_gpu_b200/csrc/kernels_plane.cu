@@ -268,7 +268,7 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   const bool multi = h->cfg.size > 1, peer = multi && h->peer_ready;
   // operator-level calls (chan_convolution) left their inputs in the LOCAL pencil fields: nothing has been
   // delivered to the plane owners, so the input side goes through the NCCL exchange even when peer stores are on
-  const bool piped = peer && !op_level && !h->tune.pre_direct && !h->tune.fwd_direct;   // the inputs arrive batch by batch (chan_rk_substep)
+  const bool piped = peer && !op_level && !h->tune.pre_direct && !h->tune.fwd_direct && h->tune.xchg_pipe;   // the inputs arrive batch by batch (chan_rk_substep)
   if (peer && !op_level && !piped) { int rc = stream_barrier(h); if (rc) return rc; }    // every rank's `pre` has delivered
   else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
   for (int f = 0; f < 6; f++) xi.src[f] = (const T2*)(multi ? h->rcv[f] : pin[f]);
