@@ -375,8 +375,10 @@ def main():
     traffic = None
     pj = os.path.join(ROOT, "profiles", "ncu_summary.json")
     if os.path.exists(pj) and world == 1:
-        js = json.load(open(pj)).get(args.config, {})
-        traffic = js.get(dom, {}).get("dram_bytes_per_launch")
+        js = json.load(open(pj)).get(args.config, {}).get(dom, {})
+        traffic = js.get("dram_bytes_per_launch")
+        if traffic and js.get("planes_in_launch"):         # captured on a full plane batch: scale to the average launch of a substep
+            traffic = int(traffic * (ny / max(stages[dom]["launches_per_substep"], 1e-9)) / js["planes_in_launch"])
     lps = max(stages[dom]["launches_per_substep"], 1e-9)
     ach = stages[dom]["GBps"]
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
