@@ -197,8 +197,9 @@ int chan_deriv_y_pencils_static(chan_handle* h, void* u_dev, long n_pencils);
  * One process per GPU: chan_ipc_export writes CHAN_IPC_BYTES bytes describing this rank's exchange
  * buffers; the host passes them to every other rank (any transport: the python launcher uses
  * torch.distributed), which calls chan_ipc_import(h, rank_of_owner, bytes).  Once every peer has been
- * imported the substep stores exchanged fields straight into the owners' buffers over NVLink from
- * inside the producing kernels, and NCCL only provides two stream-ordered barriers per substep. */
+ * imported the two exchanges of a substep are bulk peer copies over NVLink straight into the owners'
+ * buffers (one contiguous slab per field and destination, destinations rotated by rank), and NCCL only
+ * provides two stream-ordered barriers per substep. */
 #define CHAN_IPC_BYTES (9 * 64)
 int chan_ipc_export(chan_handle* h, void* bytes_out);
 int chan_ipc_import(chan_handle* h, int peer_rank, const void* bytes_in);
