@@ -87,6 +87,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       { "CHAN_TUNE_PRE_DIRECT", &h->tune.pre_direct, 0, false },
       { "CHAN_TUNE_FWD_DIRECT", &h->tune.fwd_direct, 0, false },
       { "CHAN_TUNE_XCHG_PIPE", &h->tune.xchg_pipe, 0, false },
+      { "CHAN_TUNE_XCHG_CE", &h->tune.xchg_ce, 0, false },
       { "CHAN_TUNE_LANES", &h->tune.lanes, -1, false },
       { "CHAN_TUNE_LANES_S", &h->tune.lanes_s, 4, false },
       { "CHAN_TUNE_LANES_MB", &h->tune.lanes_mb, 0, false },
@@ -140,6 +141,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
     CHAN_CUDA(h, cudaStreamCreateWithPriority(&h->xo, cudaStreamNonBlocking, hi));
   }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_xs, cudaEventDisableTiming));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_cf, cudaEventDisableTiming));
+  for (int i = 0; i < 4; i++) { CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xc[i], cudaStreamNonBlocking)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_cj[i], cudaEventDisableTiming)); }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_pre, cudaEventDisableTiming));
   for (int i = 0; i < 64; i++) { CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)); }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
@@ -199,7 +202,10 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // plane owners' buffers, and then the register kernel is forced: the thread-per-chain kernel walks the rows in order, so
   // all ranks would store into the SAME plane owner at the same time (Re_tau=1000 on 8 GPUs: 3.1 ms per substep).
   // `post`: the chain kernels win at every size measured.
-  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (2 * d.M < 148L * 256 || (cfg->size > 1 && h->tune.pre_direct)) ? 1 : 0;
+  // Round-2 sweep (profiles/sweep_r02.json): between 148*128 and 148*256 chains the thread-per-chain `pre` beats the register
+  // kernel at every NY (16641 modes: 0.111 vs 0.151 ms at NY=97, 0.73 vs 1.08 ms at NY=633), and below that the on-chip lanes
+  // kernels take over: the register kernels are picked only for in-kernel peer stores.
+  if (h->tune.pencil_seg < 0) h->tune.pencil_seg = (cfg->size > 1 && h->tune.pre_direct) ? 1 : 0;
   if (h->tune.post_deep < 0) h->tune.post_deep = (2 * d.M <= 148L * 64) ? 2 : ((2 * d.M < 148L * 128) ? 1 : 0);   // 2: three warps per 32 chains
   if (h->tune.pencil_seg && seg_supported(h)) { if ((rc = seg_setup(h))) return rc; } else h->tune.pencil_seg = 0;
   // on-chip y stage (warps per mode, lanes along y; kernels_pencil_lanes.cu): bit 0 = post, bit 1 = pre.  It needs a
@@ -228,6 +234,8 @@ extern "C" void chan_destroy(chan_handle* h) {
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   for (int i = 0; i < 64; i++) { if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]); if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]); }
   if (h->ev_xs) cudaEventDestroy(h->ev_xs);
+  if (h->ev_cf) cudaEventDestroy(h->ev_cf);
+  for (int i = 0; i < 4; i++) { if (h->ev_cj[i]) cudaEventDestroy(h->ev_cj[i]); if (h->xc[i]) cudaStreamDestroy(h->xc[i]); }
   if (h->ev_pre) cudaEventDestroy(h->ev_pre);
   if (h->xs) cudaStreamDestroy(h->xs);
   if (h->xo) cudaStreamDestroy(h->xo);

@@ -101,6 +101,7 @@ struct chan_handle {
   cudaStream_t xs;              // side stream of the plane -> pencil peer copies: batch b travels while batch b+1 is transformed
   cudaStream_t xo;              // side stream of the pencil -> plane peer copies: the rows of plane batch b+1 travel while batch b is transformed
   cudaEvent_t ev_batch[64], ev_in[64], ev_xs, ev_pre;
+  cudaStream_t xc[4]; cudaEvent_t ev_cf, ev_cj[4];      // copy-engine variant of the peer copies (CHAN_TUNE_XCHG_CE)
   int pb_rank[8], nbatch;       // plane batch of every rank (same formula everywhere) and the largest batch count of any rank
   cudaEvent_t ev_fork, ev_join;
   // state + work fields, compact plane-major, complex T
@@ -133,7 +134,7 @@ struct chan_handle {
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;   // the rank's slab [Kxl][NZ][NY] of the reference layout
   double* stat_buf;             // 4*NY sums of chan_statistics
-  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_direct, fwd_direct, xchg_pipe, lanes, lanes_s, lanes_mb; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
+  struct { int z_threads, z_xp, z_pad, x_threads, x_tk, max_radix, z_stop, x_skip, pencil_seg, seg_shape, post_pf, post_threads, post_stop, post_deep, z_fwdpack, z_inpack, pre_direct, fwd_direct, xchg_pipe, xchg_ce, lanes, lanes_s, lanes_mb; } tune;   // launch shapes (CHAN_TUNE_* env overrides)
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)

@@ -398,6 +398,22 @@ __global__ void __launch_bounds__(256) peer_scatter_kernel(ScatterArgs a) {
 static int run_scatter(chan_handle* h, ScatterArgs& a, int nf) {
   const int S = h->cfg.size;
   a.S = S; a.rank = h->cfg.rank;
+  if (h->tune.xchg_ce) {
+    // CHAN_TUNE_XCHG_CE=1: the same flat copies as cudaMemcpyAsync on four copy streams (copy engines instead of SMs, so
+    // that they can run beside the transforms without taking issue slots); same rotation of the destinations
+    const size_t cb = 2 * (size_t)h->prec;
+    cudaStream_t base = h->stream;
+    CHAN_CUDA(h, cudaEventRecord(h->ev_cf, base));
+    for (int i = 0; i < 4; i++) CHAN_CUDA(h, cudaStreamWaitEvent(h->xc[i], h->ev_cf, 0));
+    for (int z = 0; z < S; z++) {
+      const int p = (a.rank + z) % S;
+      if (!a.count[p]) continue;
+      for (int q = 0; q < nf; q++)
+        CHAN_CUDA(h, cudaMemcpyAsync((char*)a.dst[p][q] + a.dst_off[p] * cb, (const char*)a.src[q] + a.src_off[p] * cb, a.count[p] * cb, cudaMemcpyDeviceToDevice, h->xc[z & 3]));
+    }
+    for (int i = 0; i < 4; i++) { CHAN_CUDA(h, cudaEventRecord(h->ev_cj[i], h->xc[i])); CHAN_CUDA(h, cudaStreamWaitEvent(base, h->ev_cj[i], 0)); }
+    return CHAN_OK;
+  }
   // copy units of 16 bytes: one fp64 complex, or two fp32 complex when every offset and count is even
   const long per16 = h->prec == 8 ? 1 : 2;
   bool even = true;
