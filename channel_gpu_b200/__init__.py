@@ -5,4 +5,4 @@ lib/libchannel_b200.so (hand-written CUDA for sm_100a behind the C ABI of
 include/channel_b200.h).  Importing this package without that library raises:
 there is no CPU or PyTorch fallback.
 """
-from .api import Channel, ChannelError, lib_path, load_library, partition, exchange_layout, FIELDS  # noqa: F401
+from .api import Channel, ChannelError, lib_path, load_library, partition, exchange_layout, peer_put_layout, FIELDS  # noqa: F401

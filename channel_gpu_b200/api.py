@@ -73,6 +73,7 @@ def load_library():
         "chan_partition": [ci, ci, ci, C.POINTER(ci), C.POINTER(ci)],
         "chan_active_kx": [ci], "chan_active_kz": [ci],
         "chan_exchange_layout": [ci, ci, ci, ci, ci, ci, C.POINTER(C.c_long)],
+        "chan_peer_put_layout": [ci, ci, ci, ci, ci, ci, C.POINTER(C.c_long)],
     }
     for name, args in sig.items():
         f = getattr(L, name)
@@ -102,6 +103,16 @@ def exchange_layout(nx, ny, nz, size, rank, peer):
     if L.chan_exchange_layout(nx, ny, nz, size, rank, peer, out):
         raise ChannelError("bad exchange_layout arguments")
     k = ("send_off", "send_cnt", "recv_off", "recv_cnt", "peer_kx0", "peer_kxl", "peer_j0", "peer_nyl")
+    return dict(zip(k, [int(v) for v in out]))
+
+
+def peer_put_layout(nx, ny, nz, size, rank, dest):
+    """chan_peer_put_layout as a dict: the one-sided copies rank -> dest of one field, both directions."""
+    L = load_library()
+    out = (C.c_long * 6)()
+    if L.chan_peer_put_layout(nx, ny, nz, size, rank, dest, out):
+        raise ChannelError("bad peer_put_layout arguments")
+    k = ("out_src", "out_dst", "out_cnt", "back_src", "back_dst", "back_cnt")
     return dict(zip(k, [int(v) for v in out]))
 
 

@@ -39,6 +39,17 @@ extern "C" int chan_exchange_layout(int nx, int ny, int nz, int size, int rank, 
   return CHAN_OK;
 }
 
+// the same exchange seen from the sender: bulk peer copies write straight into the destination's buffers
+extern "C" int chan_peer_put_layout(int nx, int ny, int nz, int size, int rank, int dest, long* out) {
+  long L[8], Lp[8];
+  if (!out) return CHAN_ERR_ARG;
+  int rc = chan_exchange_layout(nx, ny, nz, size, rank, dest, L); if (rc) return rc;
+  if ((rc = chan_exchange_layout(nx, ny, nz, size, dest, rank, Lp))) return rc;
+  out[0] = L[0]; out[1] = Lp[2]; out[2] = L[1];      // pencil -> plane: my rows of dest's planes -> dest's block for source `rank`
+  out[3] = L[2]; out[4] = Lp[0]; out[5] = L[3];      // plane -> pencil: my block for dest's kx slab -> rows of my planes in dest's field
+  return CHAN_OK;
+}
+
 extern "C" int chan_config_default(chan_config* c) {
   if (!c) return CHAN_ERR_ARG;
   memset(c, 0, sizeof(*c));

@@ -435,7 +435,8 @@ int launch_peer_scatter(chan_handle* h, int batch) {
     const long nyl = h->part_j[p + 1] - h->part_j[p];
     long r0 = 0, nr = nyl;                                   // rows of the destination's plane batch `batch`
     if (batch >= 0) { r0 = (long)batch * h->pb_rank[p]; nr = nyl - r0 < h->pb_rank[p] ? nyl - r0 : h->pb_rank[p]; if (nr < 0) nr = 0; if (r0 > nyl) r0 = nyl; }
-    a.src_off[p] = ((long)h->part_j[p] + r0) * M; a.dst_off[p] = nyl * h->d.ikx0 * h->d.Kz + r0 * M; a.count[p] = nr * M;
+    long L[6]; chan_peer_put_layout(h->d.nx, h->d.ny, h->d.nz, h->cfg.size, h->cfg.rank, p, L);     // the layout the CPU tests check
+    a.src_off[p] = L[0] + r0 * M; a.dst_off[p] = L[1] + r0 * M; a.count[p] = nr * M;
     for (int q = 0; q < 6; q++) a.dst[p][q] = h->peer_rcv[p][q];
   }
   return run_scatter(h, a, 6);
@@ -449,7 +450,8 @@ int launch_peer_scatter_back(chan_handle* h, int js, int pb) {
   for (int q = 0; q < 3; q++) a.src[q] = h->snd[q];
   for (int p = 0; p < h->cfg.size; p++) {
     const long Mp = (long)h->seg.width[p] * h->d.Kz;
-    a.src_off[p] = h->seg.base[p] + (long)js * Mp; a.dst_off[p] = (long)(h->d.j0 + js) * Mp; a.count[p] = (long)pb * Mp;
+    long L[6]; chan_peer_put_layout(h->d.nx, h->d.ny, h->d.nz, h->cfg.size, h->cfg.rank, p, L);
+    a.src_off[p] = L[3] + (long)js * Mp; a.dst_off[p] = L[4] + (long)js * Mp; a.count[p] = (long)pb * Mp;
     for (int q = 0; q < 3; q++) a.dst[p][q] = h->peer_H[p][q];
   }
   return run_scatter(h, a, 3);

@@ -217,6 +217,14 @@ int chan_active_kx(int nx);     /* 2*floor(nx/3)+1 */
  * The plane -> pencil direction swaps the roles of [0,1] and [2,3].  Pure host arithmetic. */
 int chan_exchange_layout(int nx, int ny, int nz, int size, int rank, int peer, long* out8);
 int chan_active_kz(int nz);     /* floor((2nz-2)/3)+1 */
+/* The same exchange as ONE-SIDED copies (what the bulk NVLink peer copies do): rank `rank` writes into the buffers of
+ * `dest`.  In complex elements:
+ *   out[0], out[1], out[2]  pencil -> plane: source offset in the rank's pencil-side field, destination offset in dest's
+ *                           plane-side buffer (the block of source `rank`), count
+ *   out[3], out[4], out[5]  plane -> pencil: source offset in the rank's plane-side buffer (the block of dest's kx slab),
+ *                           destination offset in dest's pencil-side field (the rows of the rank's planes), count
+ * Rows are contiguous on both sides, so a sub-range of planes is the same triple shifted by rows * (modes of the slab). */
+int chan_peer_put_layout(int nx, int ny, int nz, int size, int rank, int dest, long* out6);
 
 #ifdef __cplusplus
 }

@@ -2,7 +2,9 @@
 # exchange variants at N GPUs, Re_tau=1000 (run under gpurun --gpus N)
 cd "$(dirname "$0")/.."
 N=${N:-8}; TAG=${TAG:-r02_n8x}; OUT=gpurun_out/$TAG; mkdir -p $OUT
-for V in "CHAN_TUNE_XCHG_PIPE=0" "CHAN_TUNE_XCHG_PIPE=1" "CHAN_TUNE_PRE_DIRECT=1 CHAN_TUNE_FWD_DIRECT=1" "CHAN_TUNE_XCHG_PIPE=0 CHAN_TUNE_FWD_DIRECT=1" $EXTRA; do
+# VARIANTS: ';'-separated lists of VAR=value (default: the four exchange designs)
+IFS=';' read -ra VARS <<< "${VARIANTS:-CHAN_TUNE_XCHG_PIPE=0;CHAN_TUNE_XCHG_PIPE=1;CHAN_TUNE_PRE_DIRECT=1 CHAN_TUNE_FWD_DIRECT=1;CHAN_TUNE_XCHG_PIPE=0 CHAN_TUNE_FWD_DIRECT=1}"
+for V in "${VARS[@]}"; do
   name=$(echo $V | tr ' =' '__')
   env $V timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29655 bench.py --gpus $N --config ${CFG:-re1000} --steps 5 --warmup 3 > $OUT/$name.json 2> $OUT/$name.err
   tail -1 $OUT/$name.json | python -c "

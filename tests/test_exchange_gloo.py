@@ -71,6 +71,30 @@ def _worker(rank, size, nx, ny, nz, port, q):
         for p, t in recv_t.items():
             back[lay[p]["send_off"]: lay[p]["send_off"] + lay[p]["send_cnt"]] = t.numpy()
         ok &= bool(np.array_equal(back, pencil))
+        # ---- the same exchange as ONE-SIDED copies (what the bulk NVLink peer copies of the GPU path do): every rank tells
+        # its destinations where it writes (chan_peer_put_layout); the destinations only apply what they are told
+        put = [cg.peer_put_layout(nx, ny, nz, size, rank, p) for p in range(size)]
+        plane2 = np.full(nyl * Kx * Kz, -1.0); back2 = np.full_like(pencil, -1.0)
+        for direction in ("out", "back"):
+            src = pencil if direction == "out" else plane
+            dst = plane2 if direction == "out" else back2
+            mine = [(put[p][direction + "_dst"], src[put[p][direction + "_src"]: put[p][direction + "_src"] + put[p][direction + "_cnt"]].copy()) for p in range(size)]
+            for p in range(size):          # all-to-all of (offset, payload) pairs through object gathers
+                gathered = [None] * size
+                dist.all_gather_object(gathered, mine[p])
+                # gathered[r] = what rank r addressed to destination p; only destination p applies it
+                if p == rank:
+                    for off, data in gathered:
+                        assert (dst[off: off + len(data)] < 0).all()          # nobody else wrote there
+                        dst[off: off + len(data)] = data
+        ok &= bool(np.array_equal(plane2, plane)) and bool(np.array_equal(back2, pencil))
+        # a sub-range of planes (one plane batch) is the same triple shifted by rows * modes of the slab
+        for p in range(size):
+            pj0, pnyl = cg.partition(ny, size, p)
+            if pnyl >= 2:
+                r0, nr = 1, pnyl - 1
+                seg = pencil[put[p]["out_src"] + r0 * M: put[p]["out_src"] + (r0 + nr) * M]
+                ok &= bool(np.array_equal(seg.reshape(nr, kxl, Kz)[:, 0, 0], _code(pj0 + r0 + np.arange(nr), kx0, 0)))
         # every rank's slabs tile the active modes and the planes
         tot = torch.tensor([float(kxl), float(nyl)])
         dist.all_reduce(tot)
