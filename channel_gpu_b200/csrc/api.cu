@@ -91,7 +91,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       { "CHAN_TUNE_PENCIL_SEG", &h->tune.pencil_seg, -1, false },
       { "CHAN_TUNE_SEG_SHAPE", &h->tune.seg_shape, 0, false },
       { "CHAN_TUNE_POST_PF", &h->tune.post_pf, 0, false },
-      { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 128, false },
+      { "CHAN_TUNE_POST_THREADS", &h->tune.post_threads, 0, false },
       { "CHAN_TUNE_POST_DEEP", &h->tune.post_deep, -1, false },
       { "CHAN_TUNE_Z_FWDPACK", &h->tune.z_fwdpack, 1, false },
       { "CHAN_TUNE_Z_INPACK", &h->tune.z_inpack, 1, false },
@@ -156,6 +156,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   for (int i = 0; i < 4; i++) { CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->xc[i], cudaStreamNonBlocking)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_cj[i], cudaEventDisableTiming)); }
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_pre, cudaEventDisableTiming));
   for (int i = 0; i < 64; i++) { CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_batch[i], cudaEventDisableTiming)); CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)); }
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_sub, cudaEventDisableTiming));
+  CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_piv, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CHAN_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   int rc;
@@ -224,7 +226,7 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   // thread-per-chain kernels: measured on B200 it wins where a rank holds few chains (many GPUs / small grids: Re_tau=550
   // on 8 GPUs: pre 0.080 -> 0.053 ms, post 0.379 -> 0.218 ms per substep) and loses on a GPU full of chains
   // (Re_tau=550 on one GPU: post 0.80 -> 1.04 ms), profiles/r02_lanes_notes.txt.  CHAN_TUNE_LANES overrides.
-  if (h->tune.lanes < 0) h->tune.lanes = (2 * d.M < 148L * 128) ? 3 : 0;
+  if (h->tune.lanes < 0) h->tune.lanes = (2 * d.M < 148L * 192) ? 3 : 0;     // 16.8 k chains at NY=193: step 3.54 -> 2.63 ms; 43.7 k at NY=385: slower
   if (h->tune.lanes && lanes_supported(h)) { if ((rc = lanes_setup(h))) return rc; } else h->tune.lanes = 0;
   CHAN_CUDA(h, cudaStreamSynchronize(h->stream));
   return CHAN_OK;
@@ -250,6 +252,8 @@ extern "C" void chan_destroy(chan_handle* h) {
   if (h->ev_pre) cudaEventDestroy(h->ev_pre);
   if (h->xs) cudaStreamDestroy(h->xs);
   if (h->xo) cudaStreamDestroy(h->xo);
+  if (h->ev_sub) cudaEventDestroy(h->ev_sub);
+  if (h->ev_piv) cudaEventDestroy(h->ev_piv);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->aux) cudaStreamDestroy(h->aux);
@@ -526,6 +530,16 @@ extern "C" int chan_get_stage_ms(chan_handle* h, double* ms, long* cnt) {
 extern "C" int chan_rk_substep(chan_handle* h, int n) {
   if (!h || n < 0 || n > 2) return CHAN_ERR_ARG;
   int rc, t;
+  if (h->tune.lanes & 1) {      // pivot tables of this substep's implicit matrix: on the side stream, beside pre and the plane stage
+    cudaStream_t main_stream = h->stream;
+    CHAN_CUDA(h, cudaEventRecord(h->ev_sub, main_stream));
+    CHAN_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_sub, 0));
+    h->stream = h->aux;
+    rc = launch_lanes_pivots(h, n);
+    h->stream = main_stream;
+    if (rc) return rc;
+    CHAN_CUDA(h, cudaEventRecord(h->ev_piv, h->aux));
+  }
   t = t_begin(h, CHAN_STAGE_PRE);
   if ((rc = (h->tune.lanes & 2) ? launch_pencil_pre_lanes(h)
           : ((h->tune.pencil_seg & 1) ? launch_pencil_pre_seg(h) : launch_pencil_pre(h)))) return rc;   // calcUW + writeUmean + d/dy + calcOmega
@@ -574,6 +588,7 @@ extern "C" int chan_rk_substep(chan_handle* h, int n) {
     if (rc) return rc;
   }
   CHAN_CUDA(h, cudaEventRecord(h->ev_join, h->aux));
+  if (h->tune.lanes & 1) CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_piv, 0));
   t = t_begin(h, CHAN_STAGE_POST);
   rc = (h->tune.lanes & 1) ? launch_pencil_post_lanes(h, n)
      : ((h->tune.pencil_seg & 2) ? launch_pencil_post_seg(h, n) : launch_pencil_post(h, n));   // RK explicit + h_v,h_g + implicit + bi-Laplacian

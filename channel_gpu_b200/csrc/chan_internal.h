@@ -103,7 +103,7 @@ struct chan_handle {
   cudaEvent_t ev_batch[64], ev_in[64], ev_xs, ev_pre;
   cudaStream_t xc[4]; cudaEvent_t ev_cf, ev_cj[4];      // copy-engine variant of the peer copies (CHAN_TUNE_XCHG_CE)
   int pb_rank[8], nbatch;       // plane batch of every rank (same formula everywhere) and the largest batch count of any rank
-  cudaEvent_t ev_fork, ev_join;
+  cudaEvent_t ev_fork, ev_join, ev_sub, ev_piv;
   // state + work fields, compact plane-major, complex T
   void *phi, *g, *v, *dv, *Rphi, *Rg;
   void *u, *w, *ox, *oy, *oz;
@@ -179,6 +179,7 @@ int lanes_supported(chan_handle* h);
 int lanes_setup(chan_handle* h);
 int launch_pencil_post_lanes(chan_handle* h, int n);
 int launch_pencil_pre_lanes(chan_handle* h);
+int launch_lanes_pivots(chan_handle* h, int n);     // pivot tables of the implicit matrix of substep n (and once the Helmholtz ones), on h->stream
 // kernels_plane.cu
 int launch_nonlinear_planes(chan_handle* h, bool op_level = false);   // u,v,w,omega -> H (in ox,oy,oz); op_level: inputs sit in the local pencil fields, step scalars untouched
 int launch_symmetrize(chan_handle* h, void* a, void* b);     // imposeSymetry on two fields

@@ -836,12 +836,20 @@ static const float kDseda[3] = { 0.0f, -17.0f / 60.0f, -5.0f / 12.0f };         
 static const float kGamma[3] = { 8.0f / 15.0f, 5.0f / 12.0f, 3.0f / 4.0f };       // RK3_kernels.cu:113
 static const float kBetha[3] = { 37.0f / 160.0f, 5.0f / 24.0f, 1.0f / 6.0f };     // RK3.c:14
 
+static int chain_block_threads(const chan_handle* h, long nchain) {
+  if (h->tune.post_threads > 0) return h->tune.post_threads;
+  (void)nchain;
+  return 128;      // one-warp blocks deal the chains more evenly but change nothing measurable (both kernels are bound by HBM as a whole)
+}
 template <typename T>
 static int pre_t(chan_handle* h) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   long nchain = 2 * h->d.M;
   PeerOut po; fill_peer_out(h, po);
-  pencil_pre_kernel<T><<<(unsigned)((nchain + 127) / 128), 128, 0, h->stream>>>(a, po);
+  // The warps of these kernels are independent (no shared memory, no block barrier): the block size only sets the granularity
+  // at which chains are dealt to the SMs (CHAN_TUNE_POST_THREADS; 32/64/128 measured equal at four grids, round 2).
+  const int bt = chain_block_threads(h, nchain);
+  pencil_pre_kernel<T><<<(unsigned)((nchain + bt - 1) / bt), bt, 0, h->stream>>>(a, po);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
@@ -851,7 +859,7 @@ static int post_t(chan_handle* h, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   a.n = n; a.alpha = (T)kAlpha[n]; a.dseda = (T)kDseda[n]; a.gammad = (T)kGamma[n]; a.betha = (T)kBetha[n];
   long nchain = 2 * h->d.M;
-  const int bt = h->tune.post_deep ? 32 : h->tune.post_threads;   // few chains: one warp per block, spread over all SMs
+  const int bt = h->tune.post_deep ? 32 : chain_block_threads(h, nchain);   // few chains: one warp per block, spread over all SMs
   const unsigned grid = (unsigned)((nchain + bt - 1) / bt);
   if (h->tune.post_deep == 2) pencil_post_roles_kernel<T><<<(unsigned)((nchain + 31) / 32), 96, 0, h->stream>>>(a);
   else if (h->tune.post_deep) pencil_post_kernel<T, true><<<grid, bt, 0, h->stream>>>(a);

@@ -712,14 +712,27 @@ static const float kDsedaL[3] = { 0.0f, -17.0f / 60.0f, -5.0f / 12.0f };        
 static const float kGammaL[3] = { 8.0f / 15.0f, 5.0f / 12.0f, 3.0f / 4.0f };       // RK3_kernels.cu:113
 static const float kBethaL[3] = { 37.0f / 160.0f, 5.0f / 24.0f, 1.0f / 6.0f };     // RK3.c:14
 
+// Pivot tables of substep n on h->stream: they depend on dt (fixed for the whole step) and on n only, so chan_rk_substep
+// issues this on the side stream at the START of the substep and the serial recurrence (0.1 ms) runs beside pre and the
+// plane stage instead of in front of post.
+template <typename T>
+static int pivots_lanes_t(chan_handle* h, int n) {
+  PArgs<T> a; fill_pencil_args<T>(h, a);
+  a.n = n; a.betha = (T)kBethaL[n];
+  LaneTabs t; fill_lane_tabs(h, t);
+  const unsigned pg = (unsigned)((h->d.M + 127) / 128);
+  if (!h->ln.pivH_ready) { pivot_lanes_kernel<T><<<pg, 128, 0, h->stream>>>(a, t, h->ln.pivH, 0); h->launches++; h->ln.pivH_ready = 1; }
+  pivot_lanes_kernel<T><<<pg, 128, 0, h->stream>>>(a, t, h->ln.pivI, 1); h->launches++;
+  CHAN_CUDA(h, cudaGetLastError());
+  return CHAN_OK;
+}
+int launch_lanes_pivots(chan_handle* h, int n) { return h->prec == 4 ? pivots_lanes_t<float>(h, n) : pivots_lanes_t<double>(h, n); }
+
 template <typename T, int S>
 static int post_lanes_t(chan_handle* h, int n) {
   PArgs<T> a; fill_pencil_args<T>(h, a);
   a.n = n; a.alpha = (T)kAlphaL[n]; a.dseda = (T)kDsedaL[n]; a.gammad = (T)kGammaL[n]; a.betha = (T)kBethaL[n];
   LaneTabs t; fill_lane_tabs(h, t);
-  const unsigned pg = (unsigned)((h->d.M + 127) / 128);
-  if (!h->ln.pivH_ready) { pivot_lanes_kernel<T><<<pg, 128, 0, h->stream>>>(a, t, h->ln.pivH, 0); h->launches++; h->ln.pivH_ready = 1; }
-  pivot_lanes_kernel<T><<<pg, 128, 0, h->stream>>>(a, t, h->ln.pivI, 1); h->launches++;
   const size_t sm = lanes_smem_bytes(h, 7, t.MB, t.NYP);
   CHAN_CUDA(h, cudaFuncSetAttribute(pencil_post_lanes_kernel<T, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   const unsigned grid = (unsigned)((h->d.M + t.MB - 1) / t.MB);
