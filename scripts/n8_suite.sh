@@ -1,6 +1,6 @@
 #!/bin/bash
-# 8-GPU measurements of one round (run under `gpurun --gpus 8`): parity of all ranks on the golden cases, Re_tau=1000 with the
-# pre-kernel variants, Re_tau=2000 (BASELINE.json configs[3]), Re_tau=550.  One JSON line per run in gpurun_out/$TAG/.
+# N-GPU measurements of one round (run under `gpurun --gpus N`, N=8 by default): parity of all ranks on the golden cases,
+# Re_tau=1000, Re_tau=2000 (BASELINE.json configs[3]), Re_tau=550 with the library defaults.  One JSON line per run in gpurun_out/$TAG/.
 cd "$(dirname "$0")/.."
 TAG=${TAG:-r02_n8}; N=${N:-8}; OUT=gpurun_out/$TAG; mkdir -p $OUT
 run() {  # name, env..., -- bench args
@@ -22,11 +22,9 @@ except Exception as e:
 PY
 }
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29654 tests/mgpu_check.py 2>&1 | grep "parity\|rank" | sort | head -12 | tee $OUT/mgpu_check.log
-run re1000_default -- --config re1000 --steps 5 --warmup 3
-run re1000_chainpre CHAN_TUNE_PENCIL_SEG=0 -- --config re1000 --steps 5 --warmup 3
-run re1000_scatter CHAN_TUNE_PENCIL_SEG=0 CHAN_TUNE_PRE_SCATTER=1 -- --config re1000 --steps 5 --warmup 3
-run re1000_lanes CHAN_TUNE_LANES=3 -- --config re1000 --steps 5 --warmup 3
+run re1000_default -- --config re1000 --steps ${STEPS:-10} --warmup 3
+if [ "${FULL:-1}" = 1 ]; then
 run re2000_default -- --config re2000 --steps 3 --warmup 3
-run re550_default -- --config re550 --steps 10 --warmup 3
-run re550_nolanes CHAN_TUNE_LANES=0 -- --config re550 --steps 10 --warmup 3
+run re550_default -- --config re550 --steps 20 --warmup 3
+fi
 nvidia-smi --query-gpu=index,memory.used,memory.total --format=csv | tee $OUT/mem.txt
