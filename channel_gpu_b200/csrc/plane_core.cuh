@@ -34,6 +34,10 @@ template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
 // chain over the segments) - a per-thread index would turn every lookup into a long-latency LDC in the
 // middle of the address computation of the loads (18 % of xfft_inv's stall samples in the ncu source view).
 FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz, int* seg_out = 0) {
+  if (sm.off0) {       // tabulated (all destination pointers are equal in this mode: the segment index is not needed)
+    if (seg_out) *seg_out = 0;
+    return (size_t)(FFT_LDG(sm.off0 + ikx) + (long)jl * FFT_LDG(sm.pitch + ikx));
+  }
   long base = sm.base[0]; int width = sm.width[0], start = sm.start[0], sg = 0;
   if (sm.nseg > 1) {
 #pragma unroll

@@ -40,7 +40,7 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   PlanT<T2> pl = plan_of<T2>(H.p);
   int kxmax = nx / 3, Kx = 2 * kxmax + 1;
   // two kx segments, as a 2-rank plane stage sees its receive buffer: rows of both at plane jl = 1
-  SegMap sm; sm.nseg = 2; int w0 = Kx / 2 + 1, w1 = Kx - w0;
+  SegMap sm; sm.nseg = 2; sm.off0 = 0; sm.pitch = 0; int w0 = Kx / 2 + 1, w1 = Kx - w0;
   sm.start[0] = 0; sm.start[1] = w0; sm.start[2] = Kx; sm.width[0] = w0; sm.width[1] = w1; sm.base[0] = 0; sm.base[1] = (long)3 * w0 * Kz;
   const int jl = 1; const size_t segtot = (size_t)3 * Kx * Kz;
   auto at = [&](int i, int kz) { return seg_offset(sm, jl, i, Kz) + kz; };
