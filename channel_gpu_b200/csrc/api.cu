@@ -202,7 +202,8 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       free(o); free(pch);
       if (rc) return rc;
       if (e != cudaSuccess) return set_err(h, CHAN_ERR_CUDA, "segment tables: %s", cudaGetErrorString(e));
-      h->seg.off0 = h->seg_off0; h->seg.pitch = h->seg_pitch;
+      // used from four segments on: with two the select chain is four instructions and as fast (measured at N=2)
+      if (cfg->size >= 4) { h->seg.off0 = h->seg_off0; h->seg.pitch = h->seg_pitch; }
     }
     const size_t pb_bytes = (size_t)d.nyl * d.Kx * d.Kz * csize(h);
     for (int f = 0; f < 6; f++) if ((rc = alloc_dev(h, &h->rcv[f], pb_bytes))) return rc;
