@@ -137,7 +137,13 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
       h->seg.base[r] = off; off += (long)d.nyl * h->seg.width[r] * d.Kz;
     }
     h->seg.start[cfg->size] = d.Kx; }
-  h->seg.off0 = 0; h->seg.pitch = 0;
+  h->seg.closed = 0;
+  if (cfg->size >= 4) {      // from four segments on the closed form beats the select chain (with two the chain is four instructions)
+    h->seg.closed = 1; h->seg.pq = d.Kx / cfg->size; h->seg.pr = d.Kx % cfg->size;
+    h->seg.mq = (unsigned)(0x100000000ull / (unsigned)h->seg.pq) + 1u; h->seg.mq1 = (unsigned)(0x100000000ull / (unsigned)(h->seg.pq + 1)) + 1u;
+    if (h->seg.pq == 1) h->seg.mq = 0;                                  // FastDiv convention: M = 0 encodes d = 1
+    h->seg.bms = (long)d.nyl * d.Kz; h->seg.bmw = 0;
+  }
   if (cfg->device >= 0) CHAN_CUDA(h, cudaSetDevice(cfg->device));
   CHAN_CUDA(h, cudaGetDevice(&h->device));
   CHAN_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -190,21 +196,6 @@ extern "C" int chan_create(const chan_config* cfg, chan_handle** out) {
   h->plane_batch = pb;
   if ((rc = alloc_dev(h, &h->Q, plane_q * pb))) return rc;
   if (cfg->size > 1) {
-    {   // per-kx tables of the plane-side addressing (SegMap)
-      long* o = (long*)malloc(sizeof(long) * d.Kx); int* pch = (int*)malloc(sizeof(int) * d.Kx);
-      if (!o || !pch) { free(o); free(pch); return set_err(h, CHAN_ERR_ALLOC, "out of host memory"); }
-      for (int s = 0; s < cfg->size; s++)
-        for (int ikx = h->seg.start[s]; ikx < h->seg.start[s + 1]; ikx++) { o[ikx] = h->seg.base[s] + (long)(ikx - h->seg.start[s]) * d.Kz; pch[ikx] = h->seg.width[s] * d.Kz; }
-      rc = alloc_dev(h, (void**)&h->seg_off0, sizeof(long) * d.Kx); if (!rc) rc = alloc_dev(h, (void**)&h->seg_pitch, sizeof(int) * d.Kx);
-      cudaError_t e = rc ? cudaSuccess : cudaMemcpyAsync(h->seg_off0, o, sizeof(long) * d.Kx, cudaMemcpyHostToDevice, h->stream);
-      if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(h->seg_pitch, pch, sizeof(int) * d.Kx, cudaMemcpyHostToDevice, h->stream);
-      if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-      free(o); free(pch);
-      if (rc) return rc;
-      if (e != cudaSuccess) return set_err(h, CHAN_ERR_CUDA, "segment tables: %s", cudaGetErrorString(e));
-      // used from four segments on: with two the select chain is four instructions and as fast (measured at N=2)
-      if (cfg->size >= 4) { h->seg.off0 = h->seg_off0; h->seg.pitch = h->seg_pitch; }
-    }
     const size_t pb_bytes = (size_t)d.nyl * d.Kx * d.Kz * csize(h);
     for (int f = 0; f < 6; f++) if ((rc = alloc_dev(h, &h->rcv[f], pb_bytes))) return rc;
     for (int f = 0; f < 3; f++) if ((rc = alloc_dev(h, &h->snd[f], pb_bytes))) return rc;
@@ -258,7 +249,7 @@ extern "C" void chan_destroy(chan_handle* h) {
   void* ptrs[] = { h->phi, h->g, h->v, h->dv, h->Rphi, h->Rg, h->u, h->w, h->ox, h->oy, h->oz, h->sA, h->sB, h->sC, h->sP,
                    h->Q, h->ytab_store, h->seg_pf, h->seg_pb, h->pivH, h->pivI, h->ln.tabs, h->ln.pivH, h->ln.pivI, h->tw_x, h->tw_z, h->invx, h->invz, h->posx, h->posz, h->mean_a, h->mean_b, h->mean_u, h->mean_N,
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->stat_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
-                   h->snd[0], h->snd[1], h->snd[2], h->barrier_word, h->seg_off0, h->seg_pitch };
+                   h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
   for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   for (int i = 0; i < 64; i++) { if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]); if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]); }

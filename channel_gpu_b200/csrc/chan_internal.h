@@ -60,9 +60,11 @@ struct FftPlan {
 // segment per source rank, as received; single GPU: one segment = the field itself).  Element
 // (row jl, ikx, kz) of segment s = start[s] <= ikx < start[s+1] lives at
 //   base[s] + (jl*width[s] + ikx - start[s])*Kz + kz      (in complex elements)
-// off0 / pitch (optional, device tables of Kx entries): the same addressing tabulated per active kx, element = off0[ikx] +
-// jl*pitch[ikx] + kz - two cached loads instead of a select chain over up to 8 segments in the FFT load / store stages
-struct SegMap { int nseg; int start[9]; int width[8]; long base[8]; const long* off0; const int* pitch; };
+// The segments are the even partition of chan_partition (the first pr slabs have pq+1 rows, the others pq) and the bases are
+// linear in (start, width): base[s] = bms*start[s] + bmw*width[s] (plane-side blocks in rank order: bms = nyl*Kz, bmw = 0;
+// peers' pencil-side fields: bms = 0, bmw = j0*Kz).  With closed = 1 the FFT load / store stages compute segment, start and
+// width of an active kx from that (two multiply-high divisions) instead of a select chain over up to 8 segments.
+struct SegMap { int nseg; int start[9]; int width[8]; long base[8]; int closed, pq, pr; unsigned mq, mq1; long bms, bmw; };
 
 // Peer-store exchange (multi-GPU): where the wall-normal `pre` kernel delivers row j of plane-stage
 // input field f — straight into the receive buffer of the rank that owns plane j, over NVLink.
@@ -133,7 +135,6 @@ struct chan_handle {
   int peer_ready; void* peer_rcv[8][6]; void* peer_H[8][3]; int* barrier_word;
   int part_kx[9], part_j[9];      // part_kx[r] = first active-kx index of rank r (part_kx[size] = Kx), same for planes
   chan::SegMap seg;               // plane-side segmentation (identical for every field)
-  long* seg_off0; int* seg_pitch; // its per-kx tables (several GPUs only)
   // boundary staging (reference layout <-> compact)
   void* io_buf; size_t io_bytes;   // the rank's slab [Kxl][NZ][NY] of the reference layout
   double* stat_buf;             // 4*NY sums of chan_statistics

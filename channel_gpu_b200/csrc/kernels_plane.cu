@@ -253,7 +253,7 @@ static void fill_z(chan_handle* h, ZArgs<T>& a) {
 template <typename T>
 static void peer_out(chan_handle* h, XArgs<T>& xf) {
   typedef typename Vec2<T>::type T2;
-  xf.seg_out.off0 = 0; xf.seg_out.pitch = 0;        // per-destination pointers and bases: the select chain, not the tables
+  xf.seg_out.bms = 0; xf.seg_out.bmw = (long)h->d.j0 * h->d.Kz;      // bases of the peers' pencil-side fields: j0 * width * Kz
   for (int g = 0; g < h->cfg.size; g++) {
     xf.seg_out.base[g] = (long)h->d.j0 * xf.seg_out.width[g] * h->d.Kz;
     for (int f = 0; f < 3; f++) xf.dst[f].p[g] = (T2*)h->peer_H[g][f];

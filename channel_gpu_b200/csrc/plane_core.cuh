@@ -34,9 +34,13 @@ template <class T2> FFT_HD PlanT<T2> plan_of(const FftPlan& p) {
 // chain over the segments) - a per-thread index would turn every lookup into a long-latency LDC in the
 // middle of the address computation of the loads (18 % of xfft_inv's stall samples in the ncu source view).
 FFT_HD size_t seg_offset(const SegMap& sm, int jl, int ikx, int Kz, int* seg_out = 0) {
-  if (sm.off0) {       // tabulated (all destination pointers are equal in this mode: the segment index is not needed)
-    if (seg_out) *seg_out = 0;
-    return (size_t)(FFT_LDG(sm.off0 + ikx) + (long)jl * FFT_LDG(sm.pitch + ikx));
+  if (sm.closed) {
+    const int big = sm.pr * (sm.pq + 1);                 // rows covered by the pr wider slabs
+    FastDiv f1, f0; f1.d = (unsigned)(sm.pq + 1); f1.M = sm.mq1; f0.d = (unsigned)sm.pq; f0.M = sm.mq;
+    const int sg = ikx < big ? fd_div(ikx, f1) : sm.pr + fd_div(ikx - big, f0);
+    const int start = sg * sm.pq + (sg < sm.pr ? sg : sm.pr), width = sm.pq + (sg < sm.pr ? 1 : 0);
+    if (seg_out) *seg_out = sg;
+    return (size_t)(sm.bms * start + sm.bmw * width + ((long)jl * width + ikx - start) * Kz);
   }
   long base = sm.base[0]; int width = sm.width[0], start = sm.start[0], sg = 0;
   if (sm.nseg > 1) {

@@ -40,7 +40,7 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   PlanT<T2> pl = plan_of<T2>(H.p);
   int kxmax = nx / 3, Kx = 2 * kxmax + 1;
   // two kx segments, as a 2-rank plane stage sees its receive buffer: rows of both at plane jl = 1
-  SegMap sm; sm.nseg = 2; sm.off0 = 0; sm.pitch = 0; int w0 = Kx / 2 + 1, w1 = Kx - w0;
+  SegMap sm; sm.nseg = 2; sm.closed = 0; int w0 = Kx / 2 + 1, w1 = Kx - w0;
   sm.start[0] = 0; sm.start[1] = w0; sm.start[2] = Kx; sm.width[0] = w0; sm.width[1] = w1; sm.base[0] = 0; sm.base[1] = (long)3 * w0 * Kz;
   const int jl = 1; const size_t segtot = (size_t)3 * Kx * Kz;
   auto at = [&](int i, int kz) { return seg_offset(sm, jl, i, Kz) + kz; };
@@ -157,8 +157,34 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   return e;
 }
 
+// the closed-form plane-side addressing (even partition of the active kx over the ranks) against the select chain
+static int test_segment_closed_form() {
+  int bad = 0;
+  for (int S = 2; S <= 8; S++)
+    for (int Kx : { 9, 21, 33, 85, 257, 683, 1365 }) {
+      if (Kx < S) continue;
+      const int Kz = 7, nyl = 5, q = Kx / S, r = Kx % S;
+      for (int mode = 0; mode < 2; mode++) {            // plane-side blocks | peers' pencil-side fields (j0 = 11)
+        SegMap a; a.nseg = S; a.closed = 0;
+        long off = 0; int st = 0;
+        for (int g = 0; g < S; g++) { int w = q + (g < r ? 1 : 0); a.start[g] = st; a.width[g] = w; a.base[g] = mode ? (long)11 * w * Kz : off; off += (long)nyl * w * Kz; st += w; }
+        a.start[S] = Kx;
+        SegMap b = a; b.closed = 1; b.pq = q; b.pr = r;
+        b.mq = q > 1 ? (unsigned)(0x100000000ull / (unsigned)q) + 1u : 0u; b.mq1 = (unsigned)(0x100000000ull / (unsigned)(q + 1)) + 1u;
+        b.bms = mode ? 0 : (long)nyl * Kz; b.bmw = mode ? (long)11 * Kz : 0;
+        for (int jl = 0; jl < nyl; jl++) for (int i = 0; i < Kx; i++) {
+          int sa = -1, sb = -1;
+          if (seg_offset(a, jl, i, Kz, &sa) != seg_offset(b, jl, i, Kz, &sb) || sa != sb) bad++;
+        }
+      }
+    }
+  printf("  segment addressing: closed form vs select chain, %d mismatches\n", bad);
+  return bad;
+}
+
 int main() {
   srand(7);
+  if (test_segment_closed_form()) return 1;
   double worst_d = 0, worst_f = 0;
   const int xs[] = { 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 384, 1024 };
   for (int n : xs) worst_d = fmax(worst_d, test_x<double2>(n, n <= 64 ? 5 : 3, 4));
