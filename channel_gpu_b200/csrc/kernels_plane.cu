@@ -22,11 +22,13 @@
 //    Q[f][plane][x][kz] is produced and consumed per plane batch sized to stay
 //    resident in the 126 MB L2.
 #include "plane_core.cuh"
+// 512 threads x 128 registers = one full register file: the bound leaves the register allocation where (256, 2) had it and
+// lets long transforms (2NZ-2 = 1536: one block per SM for shared memory) run with more than 8 warps
 #ifndef ZMAXT
-#define ZMAXT 256
+#define ZMAXT 512
 #endif
 #ifndef ZMINB
-#define ZMINB 2
+#define ZMINB 1
 #endif
 
 namespace chan {
@@ -206,7 +208,9 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   if (xp > h->d.nx / 2) xp = h->d.nx / 2;
   // one thread per item of the register-fused middle stage (m positions x xp pairs), within 128..256
   int threads = h->tune.z_threads;
-  if (threads <= 0) { threads = (m * xp + 31) / 32 * 32; threads = threads < 128 ? 128 : (threads > 256 ? 256 : threads); }
+  // (up to 384: at 2NZ-2 = 1536 only one block fits an SM and 256 threads left it with 8 warps: 14.3 -> 11.1 ms per substep
+  // on a 256x633x769 grid with 384, 11.5 with 512)
+  if (threads <= 0) { threads = (m * xp + 31) / 32 * 32; threads = threads < 128 ? 128 : (threads > 384 ? 384 : threads); }
   // Row layouts (plane_core.cuh).  Packed rows need the fused middle stage to be a single round (its barrier then
   // separates ALL reads of the inverse side from the writes of the forward side, whatever the two layouts are).
   const int nout = MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1), lout = xp * nout;
