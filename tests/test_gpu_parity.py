@@ -214,10 +214,10 @@ def test_wall_normal_sweep_vs_oracle_and_variants(cg, monkeypatch, ny):
         assert rel(regs[name], chain[name]) < (2e-10 if name == "R_ddv" else 1e-12), name
 
 
-@pytest.mark.parametrize("grid", [(48, 17, 385), (64, 17, 193), (32, 17, 65), (96, 17, 97), (48, 17, 49)])
+@pytest.mark.parametrize("grid", [(48, 17, 385), (64, 17, 193), (32, 17, 65), (96, 17, 97), (48, 17, 49), (24, 17, 769)])
 def test_z_row_layouts_bit_identical(cg, monkeypatch, grid):
     """The shared-memory row layouts of the z stage (packed rows, skews: plane_core.cuh) change no arithmetic:
-    one RK3 step with them on and off, transform lengths 2NZ-2 = 768, 384, 128, 192, 96."""
+    one RK3 step with them on and off, transform lengths 2NZ-2 = 768, 384, 128, 192, 96, 1536 (the last one runs 384 threads per block)."""
     from bench import synthetic_fields
     nx, ny, nz = grid
     ddv, gg, um = synthetic_fields(nx, ny, nz, np.complex128)
