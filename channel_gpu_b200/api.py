@@ -269,8 +269,8 @@ class Channel:
         return self.get_fields()
 
     def enable_peer_exchange(self):
-        """Multi-GPU: map every other rank's exchange buffers (CUDA IPC) so that the substep stores exchanged
-        fields straight into them over NVLink from the producing kernels.  torch.distributed carries the handles."""
+        """Multi-GPU: map every other rank's exchange buffers (CUDA IPC) so that the two exchanges of a substep are bulk
+        peer copies straight into them over NVLink.  torch.distributed carries the handles."""
         import torch.distributed as dist
         mine = C.create_string_buffer(9 * 64)
         self._ck(self.L.chan_ipc_export(self.h, mine), "chan_ipc_export")

@@ -268,7 +268,7 @@ extern "C" void chan_destroy(chan_handle* h) {
   delete h;
 }
 
-// ---- peer-store exchange set-up ---------------------------------------------------------------------
+// ---- peer-copy exchange set-up ----------------------------------------------------------------------
 extern "C" int chan_ipc_export(chan_handle* h, void* out) {
   if (!h || !out) return CHAN_ERR_ARG;
   if (h->cfg.size < 2) return set_err(h, CHAN_ERR_STATE, "chan_ipc_export needs a multi-GPU handle");
@@ -295,7 +295,7 @@ extern "C" int chan_ipc_import(chan_handle* h, int peer, const void* in) {
   if (have == h->cfg.size) {
     for (int f = 0; f < 6; f++) h->peer_rcv[h->cfg.rank][f] = h->rcv[f];
     h->peer_H[h->cfg.rank][0] = h->ox; h->peer_H[h->cfg.rank][1] = h->oy; h->peer_H[h->cfg.rank][2] = h->oz;
-    h->peer_ready = 1;      // both `pre` kernels deliver their rows with peer stores
+    h->peer_ready = 1;      // the two exchanges of a substep become bulk peer copies (kernels_pencil.cu: launch_peer_scatter*)
   }
   return CHAN_OK;
 }

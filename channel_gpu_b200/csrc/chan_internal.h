@@ -131,7 +131,7 @@ struct chan_handle {
   // multi-GPU exchange (comm.cu): NCCL communicator owned by the caller, receive buffers of the 6
   // fields entering the plane stage, send buffers of the 3 leaving it, slab boundaries of all ranks
   void* nccl_comm; void* rcv[6]; void* snd[3];
-  // peer-store exchange: CUDA-IPC-mapped buffers of the other ranks (rcv[6] and the pencil fields H1..3)
+  // peer-copy exchange: CUDA-IPC-mapped buffers of the other ranks (rcv[6] and the pencil fields H1..3)
   int peer_ready; void* peer_rcv[8][6]; void* peer_H[8][3]; int* barrier_word;
   int part_kx[9], part_j[9];      // part_kx[r] = first active-kx index of rank r (part_kx[size] = Kx), same for planes
   chan::SegMap seg;               // plane-side segmentation (identical for every field)

@@ -507,10 +507,9 @@ __global__ void __launch_bounds__(512, 1) pencil_post_lanes_kernel(PArgs<T> a, L
 // =====================================================================================================================
 // pencil_pre: (dv, g, v, <u>) -> u, w, omega_x, omega_y, omega_z: calcUW (nonLinear_kernels.cu:8-92) + writeUmean
 // (meanUevol.c:117-125) + the two deriv_Y of convolution.c:7-11 + readUtau (:14-16) + calcOmega
-// (convolution_kernels.cu:7-66).  With several GPUs the six plane-stage inputs of row j leave the staging tiles as whole
-// row segments straight into the receive buffers of the rank that owns plane j (NVLink stores: the pencil -> plane
-// transpose of channel_cuda_mpi.c:95-128); every row of the block is in flight at once, so the stores spread over all
-// destinations.
+// (convolution_kernels.cu:7-66).  With several GPUs the outputs are stored locally and a bulk peer copy delivers them
+// (launch_peer_scatter); with CHAN_TUNE_PRE_DIRECT=1 the six plane-stage inputs of row j leave the staging tiles straight into
+// the receive buffers of the rank that owns plane j instead (NVLink stores of 64-byte row pieces: measured slower).
 // =====================================================================================================================
 template <typename T, int S>
 __global__ void __launch_bounds__(512, 1) pencil_pre_lanes_kernel(PArgs<T> a, LaneTabs t, PeerOut po) {

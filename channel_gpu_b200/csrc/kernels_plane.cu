@@ -19,8 +19,9 @@
 //  * two-for-one real transforms in z: the same field at two neighbouring x is
 //    one complex line (a + i b);
 //  * the physical fields never touch HBM; the x-transformed staging
-//    Q[f][plane][x][kz] is produced and consumed per plane batch sized to stay
-//    resident in the 126 MB L2.
+//    Q[f][plane][x][kz] is produced and consumed per plane batch (as many planes
+//    as fit in 1.5 GiB: the kernels are not bandwidth-bound, large launches win
+//    over L2 residency).
 #include "plane_core.cuh"
 // 512 threads x 128 registers = one full register file: the bound leaves the register allocation where (256, 2) had it and
 // lets long transforms (2NZ-2 = 1536: one block per SM for shared memory) run with more than 8 warps
@@ -272,7 +273,7 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   void* pout[3] = { h->ox, h->oy, h->oz };
   const bool multi = h->cfg.size > 1, peer = multi && h->peer_ready;
   // operator-level calls (chan_convolution) left their inputs in the LOCAL pencil fields: nothing has been
-  // delivered to the plane owners, so the input side goes through the NCCL exchange even when peer stores are on
+  // delivered to the plane owners, so the input side goes through the NCCL exchange even when the peer copies are on
   const bool piped = peer && !op_level && !h->tune.pre_direct && !h->tune.fwd_direct && h->tune.xchg_pipe;   // the inputs arrive batch by batch (chan_rk_substep)
   if (peer && !op_level && !piped) { int rc = stream_barrier(h); if (rc) return rc; }    // every rank's `pre` has delivered
   else if (multi) { int rc = exchange_to_planes(h, 6, pin); if (rc) return rc; }
@@ -313,7 +314,7 @@ static int nonlinear_t(chan_handle* h, bool op_level) {
   }
   if (piped) CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_in[h->nbatch - 1], 0));   // every outgoing copy of this rank is done: the next `pre` may overwrite its sources
   if (peer && !direct) { CHAN_CUDA(h, cudaEventRecord(h->ev_xs, h->xs)); CHAN_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_xs, 0)); }
-  if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer stores
+  if (multi) { int rc = allreduce_umax(h); if (rc) return rc; }               // also the barrier after the peer copies
   if (multi && !peer) { int rc = exchange_to_pencils(h, 3, pout); if (rc) return rc; }
   return CHAN_OK;
 }

@@ -30,7 +30,7 @@ def main():
         ddv, gg, um = g.inputs()
         ch = cg.Channel(g.nx, g.ny, g.nz, precision=4 if g.prec == 32 else 8, device=local, rank=rank, size=size, nccl_comm=comm)
         if os.environ.get("CHAN_PEER", "1") != "0":
-            ch.enable_peer_exchange()        # fused NVLink stores; CHAN_PEER=0 keeps the NCCL send/recv exchange
+            ch.enable_peer_exchange()        # bulk NVLink peer copies; CHAN_PEER=0 keeps the NCCL send/recv exchange
         ch.RKstep(ddv, gg, n, fixed_dt=None if "freedt" in sub else g.dt, umean=um)
         Kx = 2 * (g.nx // 3) + 1
         s0, c0 = cg.partition(Kx, size, rank)

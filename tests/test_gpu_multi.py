@@ -1,6 +1,6 @@
 """Multi-GPU parity under pytest: tests/mgpu_check.py (every rank steps its kx / y-plane slab of the golden cases and
 compares it with the dumps of the reference build; operator-level convolution included) launched with torchrun on the
-GPUs of the box, with the peer-store exchange (NVLink stores from the producing kernels) and with the NCCL send/recv
+GPUs of the box, with the peer-copy exchange (bulk NVLink copies into CUDA-IPC-mapped buffers) and with the NCCL send/recv
 exchange.  Skipped on a one-GPU box; bench.py carries the same check into every N>1 line (`parity_vs_golden`)."""
 import os
 import subprocess
