@@ -22,7 +22,7 @@ except Exception as e:
 PY
 }
 [ "${CHECK:-1}" = 1 ] && timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29654 tests/mgpu_check.py 2>&1 | grep "parity\|rank" | sort | head -12 | tee $OUT/mgpu_check.log
-run re1000_default -- --config re1000 --steps ${STEPS:-10} --warmup 3
+[ "${SKIP1000:-0}" = 1 ] || run re1000_default -- --config re1000 --steps ${STEPS:-10} --warmup 3
 if [ "${FULL:-1}" != 0 ]; then
 run re2000_default -- --config re2000 --steps 3 --warmup 3
 fi
