@@ -340,6 +340,8 @@ def main():
         ms = [float(v) for v in t[:-1]]; wall = float(t[-1])
     launches = ch.launch_count() - l0
     ch.set_timing(False)
+    if cnt[4] != K:
+        raise SystemExit("bench: %d of the %d timed steps were recorded by the stage timers" % (cnt[4], K))
     clk = clocks.stop()
     step_ms = ms[4] / max(cnt[4], 1)
     value = 1e3 / step_ms

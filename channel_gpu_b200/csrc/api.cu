@@ -251,7 +251,7 @@ extern "C" void chan_destroy(chan_handle* h) {
                    h->mean_uw, h->mean_tmp, h->sc, h->io_buf, h->stat_buf, h->rcv[0], h->rcv[1], h->rcv[2], h->rcv[3], h->rcv[4], h->rcv[5],
                    h->snd[0], h->snd[1], h->snd[2], h->barrier_word };
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); i++) if (ptrs[i]) cudaFree(ptrs[i]);
-  for (int i = 0; i < 1024; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
+  for (int i = 0; i < chan_handle::EV_MAX; i++) if (h->ev0[i]) { cudaEventDestroy(h->ev0[i]); cudaEventDestroy(h->ev1[i]); }
   for (int i = 0; i < 64; i++) { if (h->ev_batch[i]) cudaEventDestroy(h->ev_batch[i]); if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]); }
   if (h->ev_xs) cudaEventDestroy(h->ev_xs);
   if (h->ev_cf) cudaEventDestroy(h->ev_cf);
@@ -509,7 +509,8 @@ extern "C" int chan_rk_init(chan_handle* h) {
 // ---- optional stage timing ----------------------------------------------------------
 namespace chan {
 int timing_begin(chan_handle* h, int stage) {
-  if (!h->timing || h->n_ev >= 1024) return -1;
+  if (!h->timing) return -1;
+  if (h->n_ev >= chan_handle::EV_MAX) { h->n_ev_dropped++; return -1; }
   int i = h->n_ev++;
   if (!h->ev0[i]) { cudaEventCreate(&h->ev0[i]); cudaEventCreate(&h->ev1[i]); }
   h->ev_stage[i] = stage;
@@ -530,7 +531,9 @@ extern "C" int chan_get_stage_ms(chan_handle* h, double* ms, long* cnt) {
     float t = 0; CHAN_CUDA(h, cudaEventElapsedTime(&t, h->ev0[i], h->ev1[i]));
     ms[h->ev_stage[i]] += t; cnt[h->ev_stage[i]]++;
   }
-  h->n_ev = 0;
+  const int dropped = h->n_ev_dropped;
+  h->n_ev = 0; h->n_ev_dropped = 0;
+  if (dropped) return set_err(h, CHAN_ERR_STATE, "%d stage instances were not timed: more than %d between two chan_get_stage_ms calls", dropped, (int)chan_handle::EV_MAX);
   return CHAN_OK;
 }
 

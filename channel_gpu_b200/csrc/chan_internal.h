@@ -142,7 +142,8 @@ struct chan_handle {
   long launches;                // kernels launched so far (bench's gpu_launches)
   long host_counter;            // steps issued (symmetry cadence, RK3.c:174)
   // optional per-stage CUDA-event timing on h->stream (bench.py's roofline figures)
-  int timing; int n_ev; cudaEvent_t ev0[1024], ev1[1024]; int ev_stage[1024];
+  enum { EV_MAX = 32768 };
+  int timing; int n_ev, n_ev_dropped; cudaEvent_t ev0[EV_MAX], ev1[EV_MAX]; int ev_stage[EV_MAX];
   char err[256];
 };
 

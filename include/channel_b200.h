@@ -90,8 +90,9 @@ long chan_launch_count(const chan_handle* h);   /* kernels launched so far */
  * 5 xfft_inv, 6 zstage, 7 xfft_fwd: the three kernels inside stage 1;
  * 8, 9 (several GPUs): the bulk peer copies pencil -> plane (inside stage 0) and plane -> pencil (inside stage 1).
  * chan_get_stage_ms synchronises, returns accumulated milliseconds and launch
- * groups per stage (arrays of CHAN_STAGE_COUNT) since the last call, and resets them.  At most 1024 stage
- * instances are recorded between two reads; later ones are not timed. */
+ * groups per stage (arrays of CHAN_STAGE_COUNT) since the last call, and resets them.  At most 32768 stage
+ * instances are recorded between two reads (a Re_tau=1000 step is 76 of them); when more were issued the call still returns
+ * the recorded ones but with CHAN_ERR_STATE, so that a caller never mistakes a partial sum for the whole. */
 enum { CHAN_STAGE_PRE = 0, CHAN_STAGE_PLANES, CHAN_STAGE_SCALAR, CHAN_STAGE_POST, CHAN_STAGE_STEP,
        CHAN_STAGE_XINV, CHAN_STAGE_Z, CHAN_STAGE_XFWD, CHAN_STAGE_XCHG_OUT, CHAN_STAGE_XCHG_BACK, CHAN_STAGE_COUNT };
 int  chan_set_timing(chan_handle* h, int on);
