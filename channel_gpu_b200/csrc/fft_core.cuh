@@ -3,7 +3,7 @@
 // same code on the CPU, emulating the threads of a block one after the other (within a phase
 // the threads touch disjoint shared-memory elements).
 //
-// Radices 2, 3, 4 are written out; 6, 8, 12, 16 are composites done entirely in registers with
+// Radices 2, 3, 4, 5 are written out; 6, 8, 10, 12, 16 are composites done entirely in registers with
 // compile-time twiddles (fft_twiddle_consts.h, generated with
 //   python -c "import math; ..."   see channel_gpu_b200/csrc/gen note in DESIGN.md section 4).
 //
@@ -68,6 +68,22 @@ template <int SIGN, class T2> struct Dft<4, SIGN, T2> {
     a[0] = cadd(t0, t2); a[2] = csub(t0, t2); a[1] = cadd(t1, t3); a[3] = csub(t1, t3);
   }
 };
+// 5 points: y_1,4 = a_0 - t/4 + (sqrt5/4)(t1 - t2) +- SIGN i (s1 d1 + s2 d2), y_2,3 = a_0 - t/4 - (sqrt5/4)(t1 - t2) +- SIGN i (s2 d1 - s1 d2)
+// with t1 = a_1 + a_4, t2 = a_2 + a_3, t = t1 + t2, d1 = a_1 - a_4, d2 = a_2 - a_3, s1 = sin 72, s2 = sin 144
+template <int SIGN, class T2> struct Dft<5, SIGN, T2> {
+  FFT_HD static void run(T2* a) {
+    typedef typename RealOf<T2>::type T;
+    const T c5 = (T)0.55901699437494742410229341718282, s1 = (T)0.95105651629515357211643933337938, s2 = (T)0.58778525229247312916870595463907;
+    T2 t1 = cadd(a[1], a[4]), t2 = cadd(a[2], a[3]), d1 = csub(a[1], a[4]), d2 = csub(a[2], a[3]);
+    T2 t = cadd(t1, t2);
+    T2 m1 = mk2<T2>(a[0].x - (T)0.25 * t.x, a[0].y - (T)0.25 * t.y);
+    T2 m2 = mk2<T2>(c5 * (t1.x - t2.x), c5 * (t1.y - t2.y));
+    T2 e1 = cadd(m1, m2), e2 = csub(m1, m2);
+    T2 o1 = muli<SIGN, T2>(mk2<T2>(s1 * d1.x + s2 * d2.x, s1 * d1.y + s2 * d2.y));
+    T2 o2 = muli<SIGN, T2>(mk2<T2>(s2 * d1.x - s1 * d2.x, s2 * d1.y - s1 * d2.y));
+    a[0] = cadd(a[0], t); a[1] = cadd(e1, o1); a[4] = csub(e1, o1); a[2] = cadd(e2, o2); a[3] = csub(e2, o2);
+  }
+};
 // R = R1*R2: n = R1*n2 + n1, k = k2 + R2*k1
 template <int R1, int R2, int SIGN, class T2> FFT_HD void dft_composite(T2* a) {
   constexpr int R = R1 * R2;
@@ -92,6 +108,7 @@ template <int R1, int R2, int SIGN, class T2> FFT_HD void dft_composite(T2* a) {
 }
 template <int SIGN, class T2> struct Dft<6, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 3, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<8, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 4, SIGN, T2>(a); } };
+template <int SIGN, class T2> struct Dft<10, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 5, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<12, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<3, 4, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<16, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<4, 4, SIGN, T2>(a); } };
 
@@ -187,7 +204,11 @@ FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
   }
 }
 
-#define FFT_DISPATCH_RADIX(r, CALL)                                                    \
+// Radix dispatch.  W5 (a compile-time flag of the calling kernel) says whether the length has a factor 5: the kernels are
+// instantiated twice, and the instances for the 2^a 3^b lengths carry no radix-5/10 code at all (with the two extra
+// cases in ONE switch the z stage and the inverse x transform of a 768 x 768 grid came out 1.5 % slower - same registers,
+// other code layout; same-box A/B, profiles/r02_radix5_ab.txt).
+#define FFT_DISPATCH_RADIX_23(r, CALL)                                                 \
   switch (r) {                                                                         \
     case 2: { constexpr int RR = 2; CALL; } break;                                     \
     case 3: { constexpr int RR = 3; CALL; } break;                                     \
@@ -197,6 +218,22 @@ FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
     case 12: { constexpr int RR = 12; CALL; } break;                                   \
     default: { constexpr int RR = 16; CALL; } break;                                   \
   }
+#define FFT_DISPATCH_RADIX_235(r, CALL)                                                \
+  switch (r) {                                                                         \
+    case 2: { constexpr int RR = 2; CALL; } break;                                     \
+    case 3: { constexpr int RR = 3; CALL; } break;                                     \
+    case 4: { constexpr int RR = 4; CALL; } break;                                     \
+    case 5: { constexpr int RR = 5; CALL; } break;                                     \
+    case 6: { constexpr int RR = 6; CALL; } break;                                     \
+    case 8: { constexpr int RR = 8; CALL; } break;                                     \
+    case 10: { constexpr int RR = 10; CALL; } break;                                   \
+    case 12: { constexpr int RR = 12; CALL; } break;                                   \
+    default: { constexpr int RR = 16; CALL; } break;                                   \
+  }
+#define FFT_DISPATCH_RADIX(W5, r, CALL)                                                \
+  do {                                                                                 \
+    if constexpr (W5) { FFT_DISPATCH_RADIX_235(r, CALL) } else { FFT_DISPATCH_RADIX_23(r, CALL) } \
+  } while (0)
 
 }  // namespace fft
 }  // namespace chan

@@ -53,7 +53,7 @@ __device__ __forceinline__ FastDiv plan_span(const FftPlan& p, int t) { FastDiv 
 
 
 // x inverse: compact spectral rows -> (zero pad) -> natural-order physical x line, still spectral in z
-template <typename T, int TK>
+template <typename T, int TK, bool W5>
 __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   T2* s = (T2*)smem_raw;
@@ -63,14 +63,14 @@ __global__ void __launch_bounds__(256, 2) xfft_inv_kernel(XArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* src = a.src[f];
   T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
+  FFT_DISPATCH_RADIX(W5, pl.r_first, (x_inv_load_stage0<T2, RR>(s, src, a.seg, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, tid, nthr)));
   __syncthreads();
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage_x<T2, +1, true, TK>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage_x<T2, +1, true, TK, W5>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(W5, pl.r_last, (x_inv_last_store<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
 }
 
 // x forward: natural-order x line -> truncated compact spectral rows
-template <typename T, int TK>
+template <typename T, int TK, bool W5>
 __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   T2* s = (T2*)smem_raw;
@@ -79,10 +79,10 @@ __global__ void __launch_bounds__(256, 2) xfft_fwd_kernel(XArgs<T> a) {
   CHAN_ABLATE_RETURN(a.dbg_skip & 2);
   const PlanT<T2> pl = plan_of<T2>(a.px);
   const T2* q = a.Q + ((size_t)(f * a.pb + jb) * a.nx) * a.Kz;
-  FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(W5, pl.r_last, (x_fwd_load_first<T2, RR>(s, q, pl, TK, kz0, a.Kz, tid, nthr)));
   __syncthreads();
-  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage_x<T2, -1, false, TK>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
-  FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
+  for (int t = pl.nstage - 2; t >= 1; t--) { plan_stage_x<T2, -1, false, TK, W5>(s, pl, a.px.radix[t], a.px.span[t], tid, nthr); __syncthreads(); }
+  FFT_DISPATCH_RADIX(W5, pl.r_first, (x_fwd_stage0_store<T2, RR>(s, a.dst[f], a.seg_out, a.j_start + jb, pl, TK, kz0, a.Kz, a.Kx, a.kxmax, a.scale, tid, nthr)));
 }
 
 // -------------------------------------------------------------------------------
@@ -104,7 +104,7 @@ __device__ __forceinline__ void atomic_max_pos(unsigned long long* slot, double 
   atomicMax(slot, (unsigned long long)__double_as_longlong(v));   // v >= 0: bit order == value order
 }
 
-template <typename T, int MODE>
+template <typename T, int MODE, bool W5>
 __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   typedef typename Vec2<T>::type T2;
   constexpr int NIN = MODE == ZM_ROTOR ? 6 : (MODE == ZM_IDENTITY ? 2 : 1);
@@ -120,10 +120,10 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   const PlanT<T2> pl = plan_of<T2>(a.pz);
   const size_t fstride = (size_t)a.pb * a.nx * a.Kz;
   T2* q0 = a.Q + ((size_t)jb * a.nx + 2 * xp0) * a.Kz;     // field 0, x = 2*xp0
-  FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, a.sha, nxp_valid, a.Kz, tid, nthr)));
+  FFT_DISPATCH_RADIX(W5, pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s, q0, fstride, pl, a.f_ng, a.XP, a.SS, a.sha, nxp_valid, a.Kz, tid, nthr)));
   __syncthreads();
   CHAN_ABLATE_RETURN(a.dbg_stop == 1);
-  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr, 1, a.sha); __syncthreads(); }
+  for (int t = 1; t + 1 < pl.nstage; t++) { plan_stage<T2, +1, true, W5>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SS, a.f_lin, ST, ST, tid, nthr, 1, a.sha); __syncthreads(); }
   CHAN_ABLATE_RETURN(a.dbg_stop == 2);
   T um[3] = { 0, 0, 0 };
   T* phys = 0; size_t pxs = 0;
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(ZMAXT, ZMINB) zstage_kernel(ZArgs<T> a) {
   }
   __syncthreads();
   if (MODE == ZM_ROTOR && tid < 3) atomicMax(a.umax_bits + tid, red[tid]);
-  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SSo, a.f_lout, NOUT, NOUT, tid, nthr, a.SKo); __syncthreads(); }
+  for (int t = pl.nstage - 2; t >= 0; t--) { plan_stage<T2, -1, false, W5>(s, pl, a.pz.radix[t], plan_span(a.pz, t), a.pz.tws[t], a.SSo, a.f_lout, NOUT, NOUT, tid, nthr, a.SKo); __syncthreads(); }
   CHAN_ABLATE_RETURN(a.dbg_stop == 4);
   z_unpack_store<T2, NIN, NOUT>(s, q0, fstride, pl, a.f_kz, a.XP, a.SSo, a.SKo, nxp_valid, tid, nthr);
 }
@@ -172,34 +172,39 @@ static int pick_x_threads(chan_handle* h, int tk) {
   return h->d.nx * tk >= 4096 ? 256 : 128;
 }
 
-template <typename T, int TK>
+template <typename T, int TK, bool W5>
 static int launch_x(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
   typedef typename Vec2<T>::type T2;
   size_t sm = (size_t)h->d.nx * TK * sizeof(T2);
   dim3 grid((h->d.Kz + TK - 1) / TK, pb, nf);
   if (inverse) {
-    CHAN_CUDA(h, cudaFuncSetAttribute(xfft_inv_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_inv_kernel<T, TK><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
+    CHAN_CUDA(h, cudaFuncSetAttribute(xfft_inv_kernel<T, TK, W5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    xfft_inv_kernel<T, TK, W5><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
   } else {
-    CHAN_CUDA(h, cudaFuncSetAttribute(xfft_fwd_kernel<T, TK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    xfft_fwd_kernel<T, TK><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
+    CHAN_CUDA(h, cudaFuncSetAttribute(xfft_fwd_kernel<T, TK, W5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    xfft_fwd_kernel<T, TK, W5><<<grid, pick_x_threads(h, TK), sm, h->stream>>>(a);
   }
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
 }
-template <typename T>
-static int launch_x_any(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
+template <typename T, bool W5>
+static int launch_x_tk(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
   typedef typename Vec2<T>::type T2;
   int tk = pick_tk(h, sizeof(T2));
-  if (tk == 8) return launch_x<T, 8>(h, inverse, a, nf, pb);
-  if (tk == 4) return launch_x<T, 4>(h, inverse, a, nf, pb);
-  if (tk == 2) return launch_x<T, 2>(h, inverse, a, nf, pb);
+  if (tk == 8) return launch_x<T, 8, W5>(h, inverse, a, nf, pb);
+  if (tk == 4) return launch_x<T, 4, W5>(h, inverse, a, nf, pb);
+  if (tk == 2) return launch_x<T, 2, W5>(h, inverse, a, nf, pb);
   return set_err(h, CHAN_ERR_ARG, "NX=%d too large for the shared-memory x transform", h->d.nx);
 }
+// the kernel instances with radix-5/10 butterflies serve the lengths with a factor 5 only (FFT_DISPATCH_RADIX)
+template <typename T>
+static int launch_x_any(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
+  return h->d.nx % 5 == 0 ? launch_x_tk<T, true>(h, inverse, a, nf, pb) : launch_x_tk<T, false>(h, inverse, a, nf, pb);
+}
 
-template <typename T, int MODE>
-static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
+template <typename T, int MODE, bool W5>
+static int launch_z_w(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   typedef typename Vec2<T>::type T2;
   // x-pairs per block: enough positions for the register-fused middle stage to occupy the block,
   // bounded by ~96 KB of shared memory so that two blocks fit on an SM
@@ -230,12 +235,17 @@ static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
   if (sm > 220 * 1024) return set_err(h, CHAN_ERR_ARG, "2NZ-2=%d too large for the shared-memory z transform", n);
   a.f_lin = make_fastdiv(xp * nin); a.f_lout = make_fastdiv(xp * (MODE == ZM_ROTOR ? 3 : (MODE == ZM_IDENTITY ? 2 : 1)));
   a.f_ng = make_fastdiv(n / h->pz.r_first); a.f_mid = make_fastdiv(m); a.f_kz = make_fastdiv(h->d.Kz);
-  CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  CHAN_CUDA(h, cudaFuncSetAttribute(zstage_kernel<T, MODE, W5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   dim3 grid((h->d.nx / 2 + xp - 1) / xp, pb);
-  zstage_kernel<T, MODE><<<grid, threads, sm, h->stream>>>(a);
+  zstage_kernel<T, MODE, W5><<<grid, threads, sm, h->stream>>>(a);
   h->launches++;
   CHAN_CUDA(h, cudaGetLastError());
   return CHAN_OK;
+}
+
+template <typename T, int MODE>
+static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
+  return h->d.nzp % 5 == 0 ? launch_z_w<T, MODE, true>(h, a, nin, pb) : launch_z_w<T, MODE, false>(h, a, nin, pb);
 }
 
 template <typename T>

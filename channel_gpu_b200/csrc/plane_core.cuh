@@ -153,14 +153,15 @@ FFT_HD void x_fwd_stage0_store(const T2* s, const SegDst<T2>& dst, const SegMap&
   }
 }
 // one shared-memory stage of plan stage t over `nlines` participating lines (see smem_stage)
-template <class T2, int SIGN, bool DIT>
+// W5: the length has a factor 5 (FFT_DISPATCH_RADIX, fft_core.cuh)
+template <class T2, int SIGN, bool DIT, bool W5>
 FFT_HD void plan_stage(T2* s, const PlanT<T2>& pl, int r, FastDiv fm, int tws, int st, FastDiv flines, int nact, int nper, int tid, int nthr, int skm = 1, int sha = -1) {
-  FFT_DISPATCH_RADIX(r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws, skm, sha)));
+  FFT_DISPATCH_RADIX(W5, r, (smem_stage<T2, RR, SIGN, DIT>(s, pl.n, fm, st, flines, nact, nper, pl.tw, tid, nthr, pl.fsk, tws, skm, sha)));
 }
 
-template <class T2, int SIGN, bool DIT, int TK>
+template <class T2, int SIGN, bool DIT, int TK, bool W5>
 FFT_HD void plan_stage_x(T2* s, const PlanT<T2>& pl, int r, int m, int tid, int nthr) {
-  FFT_DISPATCH_RADIX(r, (smem_stage_x<T2, RR, SIGN, DIT, TK>(s, pl.n, m, pl.tw, tid, nthr)));
+  FFT_DISPATCH_RADIX(W5, r, (smem_stage_x<T2, RR, SIGN, DIT, TK>(s, pl.n, m, pl.tw, tid, nthr)));
 }
 
 // =================================== z direction =================================================

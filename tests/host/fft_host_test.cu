@@ -30,9 +30,9 @@ static const int NTHR = 96;
 
 #define XSTAGE(SIGN, DIT)                                                                                         \
   switch (TK) {                                                                                                   \
-    case 2: plan_stage_x<T2, SIGN, DIT, 2>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
-    case 4: plan_stage_x<T2, SIGN, DIT, 4>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
-    default: plan_stage_x<T2, SIGN, DIT, 8>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;           \
+    case 2: plan_stage_x<T2, SIGN, DIT, 2, true>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
+    case 4: plan_stage_x<T2, SIGN, DIT, 4, true>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;            \
+    default: plan_stage_x<T2, SIGN, DIT, 8, true>(s.data(), pl, H.p.radix[t], H.p.span[t], tid, NTHR); break;           \
   }
 template <class T2> double test_x(int nx, int Kz, int TK) {
   typedef typename RealOf<T2>::type T;
@@ -48,9 +48,9 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   for (auto& v : src) { v.x = (T)frand(); v.y = (T)frand(); }
   double err = 0, nrm = 0;
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(true, pl.r_first, (x_inv_load_stage0<T2, RR>(s.data(), src.data(), sm, jl, pl, TK, kz0, Kz, Kx, kxmax, tid, NTHR))); }
     for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD XSTAGE(+1, true)
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(true, pl.r_last, (x_inv_last_store<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
   }
   for (int kz = 0; kz < Kz; kz++) for (int x = 0; x < nx; x++) {
     cd acc = 0;
@@ -62,9 +62,9 @@ template <class T2> double test_x(int nx, int Kz, int TK) {
   // forward of the physical lines must give back nx * src on the active modes
   SegDst<T2> dsts; for (int i = 0; i < 8; i++) dsts.p[i] = dst.data();
   for (int kz0 = 0; kz0 < Kz; kz0 += TK) {
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_last, (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(true, pl.r_last, (x_fwd_load_first<T2, RR>(s.data(), q.data(), pl, TK, kz0, Kz, tid, NTHR))); }
     for (int t = pl.nstage - 2; t >= 1; t--) EACH_THREAD XSTAGE(-1, false)
-    EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
+    EACH_THREAD { FFT_DISPATCH_RADIX(true, pl.r_first, (x_fwd_stage0_store<T2, RR>(s.data(), dsts, sm, jl, pl, TK, kz0, Kz, Kx, kxmax, (T)nx, tid, NTHR))); }
   }
   err = nrm = 0;
   for (int i = 0; i < Kx; i++) for (int kz = 0; kz < Kz; kz++) { size_t o = at(i, kz); err += std::norm(cd(dst[o].x - src[o].x, dst[o].y - src[o].y)); nrm += std::norm(cd(src[o].x, src[o].y)); }
@@ -108,8 +108,8 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
   T n2 = (T)7.0;
   std::vector<T> phys((size_t)nxrows * (n + 2), (T)0);
   T um[3] = { 0, 0, 0 };
-  EACH_THREAD { FFT_DISPATCH_RADIX(pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, sha, nxp_valid, Kz, tid, NTHR))); }
-  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR, 1, sha);
+  EACH_THREAD { FFT_DISPATCH_RADIX(true, pl.r_first, (z_inv_load_stage0<T2, RR, NIN>(s.data(), Q.data(), fstride, pl, make_fastdiv(n / pl.r_first), XP, SS, sha, nxp_valid, Kz, tid, NTHR))); }
+  for (int t = 1; t + 1 < pl.nstage; t++) EACH_THREAD plan_stage<T2, +1, true, true>(s.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SS, make_fastdiv(ST), ST, ST, tid, NTHR, 1, sha);
   EACH_THREAD {
     switch (pl.r_last) {
       case 2: z_mid_fused<T2, 2, MODE>(s.data(), s2.data(), pl, make_fastdiv(n / pl.r_last), XP, SS, sha, SSo, SKo, nxp_valid, n2, um, phys.data(), (size_t)(n + 2), tid, NTHR); break;
@@ -118,7 +118,7 @@ template <class T2, int MODE> double test_z(int n, int XP, int nxp_valid) {
     }
   }
   if (MODE != ZM_EXPORT) {
-    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SSo, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR, SKo);
+    for (int t = pl.nstage - 2; t >= 0; t--) EACH_THREAD plan_stage<T2, -1, false, true>(s2.data(), pl, H.p.radix[t], make_fastdiv(H.p.span[t]), H.p.tws[t], SSo, make_fastdiv(XP * NOUT), NOUT, NOUT, tid, NTHR, SKo);
     EACH_THREAD z_unpack_store<T2, NIN, NOUT>(s2.data(), Q.data(), fstride, pl, make_fastdiv(Kz), XP, SSo, SKo, nxp_valid, tid, NTHR);
   }
   // reference
@@ -186,12 +186,12 @@ int main() {
   srand(7);
   if (test_segment_closed_form()) return 1;
   double worst_d = 0, worst_f = 0;
-  const int xs[] = { 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 384, 1024 };
+  const int xs[] = { 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 384, 1024, 10, 20, 40, 50, 60, 80, 120, 160, 240, 250, 320, 640, 960, 1280 };   // from 10 on: lengths with a factor 5
   for (int n : xs) worst_d = fmax(worst_d, test_x<double2>(n, n <= 64 ? 5 : 3, 4));
   worst_d = fmax(worst_d, test_x<double2>(2048, 2, 2));
   worst_f = fmax(worst_f, test_x<float2>(384, 3, 8));
   worst_f = fmax(worst_f, test_x<float2>(128, 9, 8));
-  const int zs[] = { 8, 12, 16, 24, 32, 48, 96, 128, 384 };
+  const int zs[] = { 8, 12, 16, 24, 32, 48, 96, 128, 384, 10, 20, 30, 40, 50, 80, 160, 240, 320 };
   for (int n : zs) {
     worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(n, 2, 2));
     worst_d = fmax(worst_d, test_z<double2, ZM_IDENTITY>(n, 1, 1));
@@ -199,6 +199,11 @@ int main() {
   }
   worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(768, 1, 1));
   worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(48, 3, 2));
+  worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(640, 1, 1));
+  worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(960, 1, 1));
+  worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(100, 3, 3));
+  worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(320, 1, 1));
+  worst_f = fmax(worst_f, test_x<float2>(640, 3, 8));
   worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(384, 1, 1));
   worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(128, 2, 2));
   printf("WORST double %.3e float %.3e\n", worst_d, worst_f);

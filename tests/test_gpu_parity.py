@@ -173,6 +173,32 @@ def test_rk3_step_vs_oracle_re180(cg):
     ch.close()
 
 
+@pytest.mark.parametrize("grid", [(40, 17, 11), (80, 17, 26), (120, 17, 31), (160, 17, 81), (20, 17, 6)])
+def test_radix5_lengths_vs_oracle(cg, grid):
+    """Transform lengths with a factor 5 (radix-5 and radix-10 butterflies, fft_core.cuh): NX = 40 [8,5], 80 [16,5],
+    120 [12,10], 160 [16,10], 20 [5,4]; 2NZ-2 = 20 [5,4], 50 [5,5,2], 60 [5,3,4], 160 [10,4,4], 10 [5,2].  The u x omega
+    operator against numpy's FFTs (oracle/kmm.py:convolution) at the operator tolerance, the physical-space export, and two
+    RK3 steps against the oracle at the tolerances of the Re_tau=180 case (expf gap, module docstring)."""
+    from bench import synthetic_fields
+    nx, ny, nz = grid
+    ddv, gg, um = synthetic_fields(nx, ny, nz, np.complex128)
+    G = kmm.Grid(nx, ny, nz, np.float64)
+    ch = cg.Channel(nx, ny, nz, precision=8)
+    u, v, w = kmm.dealias(G, ddv), kmm.dealias(G, gg), kmm.dealias(G, 0.5 * ddv - 0.25j * gg)
+    want = kmm.convolution(G, u, v, w)
+    got = ch.convolution(u, v, w)
+    for a, b in zip(got, want):
+        assert rel(a, b) < 1e-12
+    assert rel(ch.fftBackwardTranspose(u), kmm.to_physical(G, u)) < 1e-12
+    S = kmm.State(G, ddv, gg, um).run(2, 2e-3)
+    ch.RKstep(ddv, gg, 2, fixed_dt=2e-3, umean=um)
+    tol = {"ddv": 5e-6, "g": 1e-8, "v": 1e-7, "dv": 1e-6, "R_ddv": 5e-6, "R_g": 1e-7}
+    for name, t in tol.items():
+        assert rel(ch.get_field(name), getattr(S, name)) < t, name
+    assert rel(ch.get_umean().real, S.mean.u) < 1e-10
+    ch.close()
+
+
 @pytest.mark.parametrize("ny", [97, 257, 385, 633])
 def test_wall_normal_sweep_vs_oracle_and_variants(cg, monkeypatch, ny):
     """BASELINE.json configs[4] (kernel sweep over NY): one RK3 step on a thin 24 x NY x 13 grid, fp64.  The
@@ -312,7 +338,7 @@ def test_full_size_properties_re550(cg):
 
 def test_error_codes(cg):
     with pytest.raises(cg.ChannelError):
-        cg.Channel(100, 21, 9)            # NX = 100 has a factor 5
+        cg.Channel(112, 21, 9)            # NX = 112 has a factor 7
     with pytest.raises(cg.ChannelError):
         cg.Channel(64, 21, 9, precision=2)
     ch = cg.Channel(64, 21, 9)
