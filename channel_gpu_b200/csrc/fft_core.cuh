@@ -3,7 +3,7 @@
 // same code on the CPU, emulating the threads of a block one after the other (within a phase
 // the threads touch disjoint shared-memory elements).
 //
-// Radices 2, 3, 4, 5 are written out; 6, 8, 10, 12, 16 are composites done entirely in registers with
+// Radices 2, 3, 4, 5, 7 are written out; 6, 8, 10, 12, 14, 16 are composites done entirely in registers with
 // compile-time twiddles (fft_twiddle_consts.h, generated with
 //   python -c "import math; ..."   see channel_gpu_b200/csrc/gen note in DESIGN.md section 4).
 //
@@ -84,6 +84,25 @@ template <int SIGN, class T2> struct Dft<5, SIGN, T2> {
     a[0] = cadd(a[0], t); a[1] = cadd(e1, o1); a[4] = csub(e1, o1); a[2] = cadd(e2, o2); a[3] = csub(e2, o2);
   }
 };
+// 7 points: with t_j = a_j + a_(7-j), d_j = a_j - a_(7-j), c_k = cos(2 pi k/7), s_k = sin(2 pi k/7):
+// y_p, y_(7-p) = a_0 + sum_j t_j c_(pj mod 7) +- SIGN i sum_j d_j s_(pj mod 7), p, j = 1..3
+template <int SIGN, class T2> struct Dft<7, SIGN, T2> {
+  FFT_HD static void run(T2* a) {
+    typedef typename RealOf<T2>::type T;
+    const T c1 = (T)0.62348980185873353052500488400424, c2 = (T)-0.22252093395631440428890256449679, c3 = (T)-0.90096886790241912623610231950745;
+    const T s1 = (T)0.78183148246802980870844452667406, s2 = (T)0.97492791218182360701813168299393, s3 = (T)0.43388373911755812047576833284836;
+    T2 t1 = cadd(a[1], a[6]), t2 = cadd(a[2], a[5]), t3 = cadd(a[3], a[4]);
+    T2 d1 = csub(a[1], a[6]), d2 = csub(a[2], a[5]), d3 = csub(a[3], a[4]);
+    T2 e1 = mk2<T2>(a[0].x + c1 * t1.x + c2 * t2.x + c3 * t3.x, a[0].y + c1 * t1.y + c2 * t2.y + c3 * t3.y);
+    T2 e2 = mk2<T2>(a[0].x + c2 * t1.x + c3 * t2.x + c1 * t3.x, a[0].y + c2 * t1.y + c3 * t2.y + c1 * t3.y);
+    T2 e3 = mk2<T2>(a[0].x + c3 * t1.x + c1 * t2.x + c2 * t3.x, a[0].y + c3 * t1.y + c1 * t2.y + c2 * t3.y);
+    T2 o1 = muli<SIGN, T2>(mk2<T2>(s1 * d1.x + s2 * d2.x + s3 * d3.x, s1 * d1.y + s2 * d2.y + s3 * d3.y));
+    T2 o2 = muli<SIGN, T2>(mk2<T2>(s2 * d1.x - s3 * d2.x - s1 * d3.x, s2 * d1.y - s3 * d2.y - s1 * d3.y));
+    T2 o3 = muli<SIGN, T2>(mk2<T2>(s3 * d1.x - s1 * d2.x + s2 * d3.x, s3 * d1.y - s1 * d2.y + s2 * d3.y));
+    a[0] = cadd(a[0], cadd(t1, cadd(t2, t3)));
+    a[1] = cadd(e1, o1); a[6] = csub(e1, o1); a[2] = cadd(e2, o2); a[5] = csub(e2, o2); a[3] = cadd(e3, o3); a[4] = csub(e3, o3);
+  }
+};
 // R = R1*R2: n = R1*n2 + n1, k = k2 + R2*k1
 template <int R1, int R2, int SIGN, class T2> FFT_HD void dft_composite(T2* a) {
   constexpr int R = R1 * R2;
@@ -110,6 +129,7 @@ template <int SIGN, class T2> struct Dft<6, SIGN, T2> { FFT_HD static void run(T
 template <int SIGN, class T2> struct Dft<8, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 4, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<10, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 5, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<12, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<3, 4, SIGN, T2>(a); } };
+template <int SIGN, class T2> struct Dft<14, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<2, 7, SIGN, T2>(a); } };
 template <int SIGN, class T2> struct Dft<16, SIGN, T2> { FFT_HD static void run(T2* a) { dft_composite<4, 4, SIGN, T2>(a); } };
 
 // ---- stage twiddles W_{mR}^{q k}, q = 1..R-1 -----------------------------------------------------
@@ -204,8 +224,8 @@ FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
   }
 }
 
-// Radix dispatch.  W5 (a compile-time flag of the calling kernel) says whether the length has a factor 5: the kernels are
-// instantiated twice, and the instances for the 2^a 3^b lengths carry no radix-5/10 code at all (with the two extra
+// Radix dispatch.  W5 (a compile-time flag of the calling kernel) says whether the length has a factor 5 or 7: the kernels
+// are instantiated twice, and the instances for the 2^a 3^b lengths carry no radix-5/7/10/14 code at all (with the two extra
 // cases in ONE switch the z stage and the inverse x transform of a 768 x 768 grid came out 1.5 % slower - same registers,
 // other code layout; same-box A/B, profiles/r02_radix5_ab.txt).
 #define FFT_DISPATCH_RADIX_23(r, CALL)                                                 \
@@ -218,21 +238,23 @@ FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
     case 12: { constexpr int RR = 12; CALL; } break;                                   \
     default: { constexpr int RR = 16; CALL; } break;                                   \
   }
-#define FFT_DISPATCH_RADIX_235(r, CALL)                                                \
+#define FFT_DISPATCH_RADIX_2357(r, CALL)                                                \
   switch (r) {                                                                         \
     case 2: { constexpr int RR = 2; CALL; } break;                                     \
     case 3: { constexpr int RR = 3; CALL; } break;                                     \
     case 4: { constexpr int RR = 4; CALL; } break;                                     \
     case 5: { constexpr int RR = 5; CALL; } break;                                     \
     case 6: { constexpr int RR = 6; CALL; } break;                                     \
+    case 7: { constexpr int RR = 7; CALL; } break;                                     \
     case 8: { constexpr int RR = 8; CALL; } break;                                     \
     case 10: { constexpr int RR = 10; CALL; } break;                                   \
     case 12: { constexpr int RR = 12; CALL; } break;                                   \
+    case 14: { constexpr int RR = 14; CALL; } break;                                   \
     default: { constexpr int RR = 16; CALL; } break;                                   \
   }
 #define FFT_DISPATCH_RADIX(W5, r, CALL)                                                \
   do {                                                                                 \
-    if constexpr (W5) { FFT_DISPATCH_RADIX_235(r, CALL) } else { FFT_DISPATCH_RADIX_23(r, CALL) } \
+    if constexpr (W5) { FFT_DISPATCH_RADIX_2357(r, CALL) } else { FFT_DISPATCH_RADIX_23(r, CALL) } \
   } while (0)
 
 }  // namespace fft

@@ -197,10 +197,10 @@ static int launch_x_tk(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb
   if (tk == 2) return launch_x<T, 2, W5>(h, inverse, a, nf, pb);
   return set_err(h, CHAN_ERR_ARG, "NX=%d too large for the shared-memory x transform", h->d.nx);
 }
-// the kernel instances with radix-5/10 butterflies serve the lengths with a factor 5 only (FFT_DISPATCH_RADIX)
+// the kernel instances with radix-5/7/10/14 butterflies serve the lengths with a factor 5 or 7 only (FFT_DISPATCH_RADIX)
 template <typename T>
 static int launch_x_any(chan_handle* h, bool inverse, XArgs<T>& a, int nf, int pb) {
-  return h->d.nx % 5 == 0 ? launch_x_tk<T, true>(h, inverse, a, nf, pb) : launch_x_tk<T, false>(h, inverse, a, nf, pb);
+  return (h->d.nx % 5 == 0 || h->d.nx % 7 == 0) ? launch_x_tk<T, true>(h, inverse, a, nf, pb) : launch_x_tk<T, false>(h, inverse, a, nf, pb);
 }
 
 template <typename T, int MODE, bool W5>
@@ -245,7 +245,7 @@ static int launch_z_w(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
 
 template <typename T, int MODE>
 static int launch_z(chan_handle* h, ZArgs<T>& a, int nin, int pb) {
-  return h->d.nzp % 5 == 0 ? launch_z_w<T, MODE, true>(h, a, nin, pb) : launch_z_w<T, MODE, false>(h, a, nin, pb);
+  return (h->d.nzp % 5 == 0 || h->d.nzp % 7 == 0) ? launch_z_w<T, MODE, true>(h, a, nin, pb) : launch_z_w<T, MODE, false>(h, a, nin, pb);
 }
 
 template <typename T>

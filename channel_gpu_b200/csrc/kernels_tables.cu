@@ -103,12 +103,12 @@ static int upload_perms(chan_handle* h, FftPlan& p, int** dinv, int** dpos) {
   return CHAN_OK;
 }
 
-// Radix schedule: fewest stages (>= 2) out of {16,12,10,8,6,5,4,3,2}, then the largest smallest radix.
-// (5 and 10 only ever divide lengths with a factor 5: the schedules of the 2^a 3^b lengths are what they were.)
+// Radix schedule: fewest stages (>= 2) out of {16,14,12,10,8,7,6,5,4,3,2}, then the largest smallest radix.
+// (5, 7, 10 and 14 only ever divide lengths with such a factor: the schedules of the 2^a 3^b lengths are what they were.)
 // small_last: the last stage is fused with the pointwise product in z and must be 4, 3 or 2
 // (6 lines x r_L complex values live in registers).
 static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int* bestmin, bool small_last, int max_radix) {
-  static const int cand[9] = { 16, 12, 10, 8, 6, 5, 4, 3, 2 };
+  static const int cand[11] = { 16, 14, 12, 10, 8, 7, 6, 5, 4, 3, 2 };
   if (n == 1) {
     if (depth != maxdepth) return false;
     int mn = 99; bool has_small = false;
@@ -119,7 +119,7 @@ static bool plan_search(int n, int depth, int maxdepth, int* cur, int* best, int
   }
   if (depth >= maxdepth) return false;
   bool found = false;
-  for (int c = 0; c < 9; c++) {
+  for (int c = 0; c < 11; c++) {
     int r = cand[c];
     if (n % r || r > max_radix) continue;
     if (depth > 0 && r > cur[depth - 1]) continue;      // non-increasing: each multiset once
@@ -220,7 +220,7 @@ static int build_tables_t(chan_handle* h) {
   make_plan(&h->px, h->d.nx, false, h->tune.max_radix);
   make_plan(&h->pz, h->d.nzp, true, h->tune.max_radix);
   if (h->px.n < 0 || h->pz.n < 0)
-    return set_err(h, CHAN_ERR_ARG, "NX=%d and 2NZ-2=%d must factor into 2s, 3s and 5s", h->d.nx, h->d.nzp);
+    return set_err(h, CHAN_ERR_ARG, "NX=%d and 2NZ-2=%d must factor into 2s, 3s, 5s and 7s", h->d.nx, h->d.nzp);
   int rc = upload_twiddles<T>(h, h->d.nx, &h->tw_x); if (rc) return rc;
   rc = upload_twiddles<T>(h, h->d.nzp, &h->tw_z); if (rc) return rc;
   h->px.tw = h->tw_x; h->pz.tw = h->tw_z;

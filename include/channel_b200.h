@@ -72,8 +72,8 @@ enum { CHAN_F_DDV = 0, CHAN_F_G, CHAN_F_V, CHAN_F_DV, CHAN_F_R_DDV, CHAN_F_R_G,
 
 int  chan_config_default(chan_config* cfg);
 /* setUp (setUp.c:3-29) + setRK3 (RK3.c:17-50) + setRKmean (meanUevol.c:43-84).
- * Sizes: NX and 2NZ-2 must factor into 2s, 3s and 5s (the hand-written FFTs have radices 2, 3, 4, 5 and their
- * composites 6, 8, 10, 12, 16; the reference, through cuFFT, takes any size), NX even, NX >= 8, NY >= 8, NZ >= 5; NX*8 and
+ * Sizes: NX and 2NZ-2 must factor into 2s, 3s, 5s and 7s (the hand-written FFTs have radices 2, 3, 4, 5, 7 and their
+ * composites 6, 8, 10, 12, 14, 16; the reference, through cuFFT, takes any size), NX even, NX >= 8, NY >= 8, NZ >= 5; NX*8 and
  * (2NZ-2)*7 complex elements of the state type must fit the 200 KB / 220 KB shared-memory tiles of the x / z
  * transforms (NX <= 12800, 2NZ-2 <= 2011 in fp64).
  * Ownership on failure: whenever *out comes back non-NULL the caller owns it, also when the return code is

@@ -186,12 +186,12 @@ int main() {
   srand(7);
   if (test_segment_closed_form()) return 1;
   double worst_d = 0, worst_f = 0;
-  const int xs[] = { 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 384, 1024, 10, 20, 40, 50, 60, 80, 120, 160, 240, 250, 320, 640, 960, 1280 };   // from 10 on: lengths with a factor 5
+  const int xs[] = { 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 384, 1024, 10, 20, 40, 50, 60, 80, 120, 160, 240, 250, 320, 640, 960, 1280, 14, 28, 56, 70, 112, 196, 224, 448, 896 };   // from 10 on: lengths with a factor 5 or 7
   for (int n : xs) worst_d = fmax(worst_d, test_x<double2>(n, n <= 64 ? 5 : 3, 4));
   worst_d = fmax(worst_d, test_x<double2>(2048, 2, 2));
   worst_f = fmax(worst_f, test_x<float2>(384, 3, 8));
   worst_f = fmax(worst_f, test_x<float2>(128, 9, 8));
-  const int zs[] = { 8, 12, 16, 24, 32, 48, 96, 128, 384, 10, 20, 30, 40, 50, 80, 160, 240, 320 };
+  const int zs[] = { 8, 12, 16, 24, 32, 48, 96, 128, 384, 10, 20, 30, 40, 50, 80, 160, 240, 320, 14, 28, 42, 56, 98, 112, 140, 224 };
   for (int n : zs) {
     worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(n, 2, 2));
     worst_d = fmax(worst_d, test_z<double2, ZM_IDENTITY>(n, 1, 1));
@@ -202,6 +202,9 @@ int main() {
   worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(640, 1, 1));
   worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(960, 1, 1));
   worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(100, 3, 3));
+  worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(448, 1, 1));
+  worst_d = fmax(worst_d, test_z<double2, ZM_ROTOR>(896, 1, 1));
+  worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(224, 2, 2));
   worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(320, 1, 1));
   worst_f = fmax(worst_f, test_x<float2>(640, 3, 8));
   worst_f = fmax(worst_f, test_z<float2, ZM_ROTOR>(384, 1, 1));

@@ -173,10 +173,11 @@ def test_rk3_step_vs_oracle_re180(cg):
     ch.close()
 
 
-@pytest.mark.parametrize("grid", [(40, 17, 11), (80, 17, 26), (120, 17, 31), (160, 17, 81), (20, 17, 6)])
-def test_radix5_lengths_vs_oracle(cg, grid):
-    """Transform lengths with a factor 5 (radix-5 and radix-10 butterflies, fft_core.cuh): NX = 40 [8,5], 80 [16,5],
-    120 [12,10], 160 [16,10], 20 [5,4]; 2NZ-2 = 20 [5,4], 50 [5,5,2], 60 [5,3,4], 160 [10,4,4], 10 [5,2].  The u x omega
+@pytest.mark.parametrize("grid", [(40, 17, 11), (80, 17, 26), (120, 17, 31), (160, 17, 81), (20, 17, 6), (56, 17, 8), (112, 17, 29), (28, 17, 50), (70, 17, 71)])
+def test_radix5_and_7_lengths_vs_oracle(cg, grid):
+    """Transform lengths with a factor 5 or 7 (radix-5/7/10/14 butterflies, fft_core.cuh): NX = 40 [8,5], 80 [16,5],
+    120 [12,10], 160 [16,10], 20 [5,4], 56 [8,7], 112 [14,8], 28 [7,4], 70 [10,7]; 2NZ-2 = 20 [5,4], 50 [5,5,2], 60 [5,3,4],
+    160 [10,4,4], 10 [5,2], 14 [7,2], 56 [14,4], 98 [7,7,2], 140 [7,5,4].  The u x omega
     operator against numpy's FFTs (oracle/kmm.py:convolution) at the operator tolerance, the physical-space export, and two
     RK3 steps against the oracle at the tolerances of the Re_tau=180 case (expf gap, module docstring)."""
     from bench import synthetic_fields
@@ -338,7 +339,7 @@ def test_full_size_properties_re550(cg):
 
 def test_error_codes(cg):
     with pytest.raises(cg.ChannelError):
-        cg.Channel(112, 21, 9)            # NX = 112 has a factor 7
+        cg.Channel(88, 21, 9)             # NX = 88 has a factor 11
     with pytest.raises(cg.ChannelError):
         cg.Channel(64, 21, 9, precision=2)
     ch = cg.Channel(64, 21, 9)

@@ -8,8 +8,8 @@ libchannel_b200 (C ABI) and every field is compared:
     (the first runs with dt = 0, RK3.c:114, so two are needed to exercise the implicit solves) at <= 1e-11
     relative L2 — the north_star bound.  At NY >= 97 the library picks other kernel instances than on the toy
     grids of tests/golden (batched thread-per-chain sweeps, multi-round FFT stages, the on-chip warp-per-chain
-    y stage), which is the point of these cases; 160x33x41 (NX = 160 = 16*10, 2NZ-2 = 80 = 5*4*4) does the same for the
-    radix-5 and radix-10 butterflies, which no BASELINE grid uses;
+    y stage), which is the point of these cases; 160x33x41 (NX = 160 = 16*10, 2NZ-2 = 80 = 5*4*4) and 112x33x29
+    (NX = 112 = 14*8, 2NZ-2 = 56 = 14*4) do the same for the radix-5/10 and radix-7/14 butterflies, which no BASELINE grid uses;
   * 128x97x65 with the fp32 state as shipped: one step at <= 1e-5;
   * the reference's own initial field (io.c:74-98: every entry -0.5*NX): one step, compared where it stays finite;
   * BASELINE.json configs[0] window: 100 steps at 128x97x65 from the seeded field through the run.conf-driven C
@@ -84,7 +84,7 @@ def sample_pencils(nx, nz, n=64):
     return ii[pick], kk[pick]
 
 
-@pytest.mark.parametrize("grid", [(128, 97, 65), (384, 193, 193), (160, 33, 41)])
+@pytest.mark.parametrize("grid", [(128, 97, 65), (384, 193, 193), (160, 33, 41), (112, 33, 29)])
 def test_two_steps_fp64_vs_reference_build(grid, short_tmp):
     import channel_gpu_b200 as cg
     nx, ny, nz = grid
