@@ -226,7 +226,7 @@ FFT_HD void smem_stage_x(T2* s, int n, int m, const T2* tw, int tid, int nthr) {
 
 // Radix dispatch.  W5 (a compile-time flag of the calling kernel) says whether the length has a factor 5 or 7: the kernels
 // are instantiated twice, and the instances for the 2^a 3^b lengths carry no radix-5/7/10/14 code at all (with the two extra
-// cases in ONE switch the z stage and the inverse x transform of a 768 x 768 grid came out 1.5 % slower - same registers,
+// cases in ONE switch the z stage and the inverse x transform of the 1024 x 385 x 768 grid came out 1.5 % slower - same registers,
 // other code layout; same-box A/B, profiles/r02_radix5_ab.txt).
 #define FFT_DISPATCH_RADIX_23(r, CALL)                                                 \
   switch (r) {                                                                         \
