@@ -127,7 +127,7 @@ def test_two_steps_fp64_vs_reference_build(grid, short_tmp):
     ch.close()
 
 
-@pytest.mark.parametrize("grid", [(128, 97, 65), (384, 193, 193)])
+@pytest.mark.parametrize("grid", [(128, 97, 65), (384, 193, 193), (160, 33, 41), (112, 33, 29)])
 def test_sampled_fixture(grid):
     """The same two-step comparison against the committed sample of the reference dump (64 pencils per field and
     the field norms): runs wherever the library runs."""
